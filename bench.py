@@ -1,0 +1,332 @@
+#!/usr/bin/env python
+"""bench.py — throughput of the Monte-Carlo PDA evaluation (BASELINE.json metric:
+burst-samples/s) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--cfg 2]
+
+A "step" is one evaluation of one parameter vector over the whole synthetic burst set
+(config 2: 1e5 bursts x 100 repeats = 1e7 burst-samples per GPU).  At N > 1 (torchrun) every
+rank holds its own 1e5-burst shard of one N x 1e5-burst dataset (weak scaling) and each step
+all-reduces the histogram with NCCL before chi-square (burst-split mode).
+
+  value     device-timed (CUDA events on the launching stream), inputs resident in HBM
+  e2e       the same step through the public API with host buffers: set_nstates/set_params/
+            setBurstBd/run_kernel + wait + read chi2 and histogram from pinned host memory
+  roofline  HBM roofline of the evaluation kernel (algorithmic bytes 36 B/burst + 16 B/photon)
+            plus the instruction-issue figure the north star asks for (`issue`)
+  cpu_baseline  the checker (oracle/_ref = the reference's own kernel source built for the
+            host, else the C port) timed on this box's host cores on a bounded sample
+
+--impl reference times only that CPU path (rank 0), same metric/config.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from gsmfretda_b200 import synth  # noqa: E402
+
+NB, LEFT_PAD = 200, 2
+SEED = 20261104
+# algorithmic thread-instructions per burst-sample, frozen from SURVEY.md §8(d) before optimisation
+ALGO_OPS = {1: 400.0, 2: 610.0, 3: 1230.0, 4: 610.0, 5: 980.0}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)", float(d.get("sm_max_mhz", 1965.0))
+    return 6650.0, "fallback (B200_PROFILING.md)", 1965.0
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); smax.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": float(max(smax)) if smax else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_leg(w, sample_bursts, R, seconds_hint=12.0):
+    """Time the reference's CPU path on a bounded sample -> dict for `cpu_baseline`."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle_py
+    O = oracle_py.Oracle()
+    cores = O.num_threads()
+    use_ref = oracle_py.have_ref()
+    Rr = R
+    note = ""
+    if use_ref:
+        Rf = oracle_py.Ref()
+        Rr = 1 << (int(R).bit_length() - 1)  # mc::set_reSampleTimes rounds down to 2^k (mc.cu:316)
+        if Rr != R:
+            note = f"; the reference needs a power-of-two reSampleTimes: {R} -> {Rr}"
+    b = w.bursts(n_bursts=sample_bursts)
+    ohist = O.observed_hist(b, NB)
+
+    def once(nb_):
+        t0 = time.perf_counter()
+        if use_ref:
+            e = Rf.mc_kernel(b, w.n_states, w.args[0], Rr, SEED & 0xFFFFFFFF, 1, N=nb_)
+            h = O.hist(e, NB)                     # streamWorker's host histogram + chi-square
+            O.chi2(ohist, h, NB, Rr, LEFT_PAD, w.n_states)
+        else:
+            O.eval_chi2(b, w.n_states, w.args[0], Rr, SEED & 0xFFFFFFFF, 1, ohist, NB, LEFT_PAD, 0, nb_)
+        return time.perf_counter() - t0
+
+    probe_n = max(1, min(sample_bursts, 2000))
+    once(probe_n)
+    dt = once(probe_n)
+    nb_ = int(max(probe_n, min(sample_bursts, probe_n * seconds_hint / max(dt, 1e-6))))
+    dt1 = once(nb_)
+    reps = int(max(1, min(64, round(seconds_hint / max(dt1, 1e-6)))))  # whole evaluations, back to back
+    dt = dt1 if reps == 1 else sum(once(nb_) for _ in range(reps))
+    samples = nb_ * Rr * reps
+    return {"value": samples / dt, "unit": "burst-samples/s", "cores": cores,
+            "kind": "reference" if use_ref else "port",
+            "sample": f"{reps} evaluation(s) of {nb_} bursts x {Rr} repeats of {w.name} ({samples} burst-samples, {dt:.2f} s, "
+                      f"{'reference mc_kernel source built for the host (oracle/_ref)' if use_ref else 'C port (oracle/pda_oracle.c)'}"
+                      f" + host histogram + chi-square, OpenMP over samples{note})",
+            "_samples": samples, "_seconds": dt}
+
+
+def run_reference(args, w, rank):
+    if rank != 0:
+        return
+    per_step = []
+    leg = None
+    for i in range(args.warmup + args.steps):
+        leg = cpu_leg(w, min(w.n_bursts, 100000), w.R, seconds_hint=5.0 if i >= args.warmup else 1.0)
+        if i >= args.warmup:
+            per_step.append(leg)
+    tot_samples = sum(l["_samples"] for l in per_step)
+    tot_s = sum(l["_seconds"] for l in per_step)
+    val = tot_samples / tot_s
+    cb = {k: v for k, v in leg.items() if not k.startswith("_")}
+    cb["value"] = val
+    out = {"impl": "reference", "metric": "burst-samples/s", "value": val, "unit": "burst-samples/s",
+           "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": 1e3 * tot_s / max(1, len(per_step)), "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "f32 walk + f64 binomial", "data": "synthetic",
+           "config": {"workload": w.name, "bursts": w.n_bursts, "repeats": w.R, "states": w.n_states,
+                      "param_vectors": 1, "note": "CPU path of the reference on a bounded sample per step"},
+           "cpu_baseline": cb,
+           "e2e": {"value": val, "unit": "burst-samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cfg", type=int, default=2)
+    ap.add_argument("--bursts", type=int, default=None, help="override bursts per GPU")
+    ap.add_argument("--repeats", type=int, default=None)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    w = synth.workload(args.cfg, n_bursts=args.bursts, R=args.repeats)
+    if args.impl == "reference":
+        run_reference(args, w, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from gsmfretda_b200 import capi
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- data: every rank owns one shard of a world x B burst dataset ------------------
+    b = w.bursts(seed=w.seed + 1000 * rank)
+    B, R, n = b.n_bursts, w.R, w.n_states
+    arg0 = w.args[0]
+    mc = capi.Mc(local_rank, 2)
+    mc.set_gpuid()
+    mc.set_reSampleTimes(R)
+    mc.set_seed(SEED)
+    mc.set_hist(NB, LEFT_PAD)
+    mc.init_bursts(b, g_offset=rank * B)
+    if world > 1:
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(capi.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        mc.comm_init(bytes(idt.cpu().numpy().tobytes()), rank, world)
+        oh = torch.from_numpy(mc.observed_hist()).cuda()
+        dist.all_reduce(oh)  # counts < 2^24: exact in f32
+        mc.set_observed_hist(oh.cpu().numpy())
+    samples_rank = B * R
+    samples_job = samples_rank * world
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def step_resident():
+        flush.zero_()
+        torch.cuda.synchronize()
+        mc.run_resident(B, 0)
+        mc.sync(0)
+        return mc.elapsed_ms(0)
+
+    def step_e2e():
+        mc.set_nstates(n, 0)
+        mc.set_params(n, 0, arg0)
+        Ns = mc.setBurstBd(0, -1, 0)
+        mc.run_kernel(Ns, 0)
+        while not mc.streamQuery(0):
+            pass
+        return mc.chi2(0), mc.hist(0, 0)
+
+    # resident parameters for the device-timed leg
+    chi2_first, hist_first = mc.evaluate(n, arg0, sid=0)
+    assert int(hist_first.sum()) == samples_job, (int(hist_first.sum()), samples_job)
+    for _ in range(args.warmup):
+        step_resident()
+    l0 = mc.launch_count()
+    clocks = ClockSampler(local_rank)
+    barrier()
+    clocks.start()
+    t_wall0 = time.perf_counter()
+    ms = [step_resident() for _ in range(args.steps)]
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    clk = clocks.stop()
+    launches = mc.launch_count() - l0
+    dev_ms = float(sum(ms))
+
+    # end to end through the public API, host buffers in and out
+    for _ in range(args.warmup):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        chi2_last, hist_last = step_e2e()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    assert int(hist_last.sum()) == samples_job
+
+    if world > 1:
+        t = torch.tensor([dev_ms, e2e_s, t_wall], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms, e2e_s, t_wall = (float(x) for x in t.cpu())
+
+    if rank == 0:
+        peak, peak_src, sm_max = measured_peaks()
+        ms_per_step = dev_ms / args.steps
+        value = samples_job * args.steps / (dev_ms * 1e-3)
+        algo_bytes = b.algorithmic_bytes()
+        achieved = algo_bytes / (ms_per_step * 1e-3) / 1e9
+        f_clk = (clk.get("sm_mhz") or sm_max) * 1e6
+        issue_peak = 148 * 128 * f_clk
+        per_gpu = value / world
+        out = {
+            "metric": "burst-samples/s", "value": value, "unit": "burst-samples/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 walk + f64 binomial (replay arithmetic), u32/u64 histogram",
+            "data": "synthetic",
+            "config": {"workload": w.name, "bursts_per_gpu": B, "photons_per_gpu": b.n_photons,
+                       "repeats": R, "states": n, "param_vectors": 1, "hist_bins": NB,
+                       "sharding": "single GPU" if world == 1 else f"burst-split x{world}, NCCL all-reduce of the histogram",
+                       "l2": "256 MiB buffer written between timed iterations (L2 flush)",
+                       "timing": "CUDA events on the launching stream per step, summed; max over ranks",
+                       "photon_layout": "packed 4 B/photon" if mc.is_packed() else "raw 16 B/photon"},
+            "param_evals_per_s": args.steps * 1.0 / (dev_ms * 1e-3),
+            "wall_s_timed_region": t_wall,
+            "e2e": {"value": samples_job * args.steps / e2e_s, "unit": "burst-samples/s",
+                    "h2d_bytes_per_step": 612, "d2h_bytes_per_step": 16 + (NB + 2) * 8 + 4,
+                    "ms_per_step": 1e3 * e2e_s / args.steps,
+                    "api": "Mc.set_nstates/set_params/setBurstBd/run_kernel/streamQuery + chi2()/hist()"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": algo_bytes,
+                         "note": "the kernel is instruction-issue bound, not HBM bound: see `issue`"},
+            "issue": {"algorithmic_thread_ops_per_sample": ALGO_OPS[args.cfg],
+                      "achieved_thread_ops_per_s": per_gpu * ALGO_OPS[args.cfg],
+                      "peak_thread_ops_per_s": issue_peak, "frac": per_gpu * ALGO_OPS[args.cfg] / issue_peak,
+                      "sm_clock_hz": f_clk, "note": "148 SMs x 128 lanes x SM clock during the run"},
+            "clocks": clk,
+            "chi2": chi2_last,
+        }
+        if not args.no_cpu:
+            cb = cpu_leg(w, min(B, 100000), R, seconds_hint=12.0)
+            out["cpu_baseline"] = {k: v for k, v in cb.items() if not k.startswith("_")}
+        print(json.dumps(out), flush=True)
+    mc.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,95 @@
+// pda_kernels.h — launch interface between the C-ABI runtime (gsmfret_c.cu) and the
+// sm_100a kernels (pda_kernels.cu).  Internal; the public boundary is include/gsmfret_c.h.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace pda {
+
+constexpr int kMaxStates = 8;
+
+// One burst, 32 bytes, read with two 16-byte loads (role of the reference's five parallel
+// per-burst arrays start/stop/istart/phCount/T, /root/reference/src/mc.cu:456-521).
+struct __align__(16) BurstRec {
+    int64_t start;
+    int64_t stop;
+    float T;
+    int32_t ph;
+    int64_t off;  // first photon: index into the packed stream (multiple of 4) or into burst_ad/dd
+};
+static_assert(sizeof(BurstRec) == 32, "BurstRec must be 32 bytes");
+
+// One parameter vector as mc::set_params leaves it on the device
+// (/root/reference/src/mc.cu:790-829): E, v, K, P_i2j, p.
+struct ParamRaw {
+    int32_t n;
+    float E[8];
+    float v[8];
+    float K[64];      // column-major n x n, K(i,j) = rate j -> i
+    float P_i2j[64];  // column-major n x n
+    float p[8];       // unnormalised inflow rates
+};
+
+struct EvalArgs {
+    const BurstRec* bursts;
+    const int32_t* pk;         // packed photons, (rel_tick << 2) | acceptor << 1 | donor ; or null
+    const int64_t* ad;         // raw burst_ad / burst_dd (fallback layout); or null
+    const int64_t* dd;
+    const ParamRaw* params;    // [P]
+    const float* ohist;        // [nb] observed counts as float
+    unsigned long long* whist; // [P][nb+2] working histogram, zero on entry, zero on exit if finalize
+    unsigned long long* hist_out;  // [P][nb+2]
+    float* chi2_out;           // [P]
+    unsigned long long* flags_out; // [1] error flags of the run
+    unsigned long long* counters;  // [0] tile ticket, [1] finished blocks, [2] error flags
+    float* mcE;                // optional [P][N*R]
+    long long* sum_ai;         // optional [P][N*R]
+    int32_t* n_steps;          // optional [P][N*R]
+    int64_t b0;                // first burst evaluated
+    int64_t N;                 // bursts evaluated
+    int64_t g_offset;          // global burst id of local burst 0 (burst-split sharding)
+    int32_t R;
+    int32_t P;
+    int32_t nb;
+    int32_t left_pad;
+    int32_t finalize;          // 1: the last block reduces chi2 and resets the working set
+    uint32_t seed;
+    uint32_t epoch0;           // parameter vector p draws with epoch0 + p
+    float clk_p, bg_ad_rate, bg_dd_rate;
+};
+
+struct LaunchCfg {
+    int grid;
+    int block;
+};
+
+// how many blocks to launch (persistent grid: SMs x resident blocks)
+LaunchCfg eval_launch_cfg(int device, bool packed, bool with_bg);
+cudaError_t launch_eval(const EvalArgs& a, bool packed, bool with_bg, LaunchCfg cfg, cudaStream_t s);
+// chi2 + copy-out + reset of the working histogram (used after a cross-GPU reduction)
+cudaError_t launch_finalize(const EvalArgs& a, cudaStream_t s);
+
+// one-time data preparation
+struct PackArgs {
+    const int64_t* start; const int64_t* stop; const int64_t* istart; const int32_t* ph; const float* T;
+    const int64_t* ad; const int64_t* dd;
+    const int64_t* poff;     // [B] packed offset of each burst (multiple of 4)
+    BurstRec* bursts;        // out
+    int32_t* pk;             // out, may be null (raw layout: bursts only)
+    unsigned int* bad;       // out: number of photons that do not fit the packed layout
+    int64_t B;
+};
+cudaError_t launch_pack(const PackArgs& a, cudaStream_t s);
+cudaError_t launch_hist_f32(const float* x, int64_t n, int nb, unsigned long long* hist, cudaStream_t s);
+cudaError_t launch_u64_to_f32(const unsigned long long* in, float* out, int n, cudaStream_t s);
+
+// primitive probes for the test-suite (one draw per element, through the device code)
+struct ProbeArgs {
+    int what; int64_t n; int ni; int nj;
+    const uint32_t* w0; const uint32_t* w1; const float* f0; const float* f1; const double* d0;
+    const int32_t* i0;
+    uint32_t* ou; float* of; double* od; long long* ol; int32_t* oi;
+};
+cudaError_t launch_probe(const ProbeArgs& a, cudaStream_t s);
+
+}  // namespace pda

@@ -1,0 +1,161 @@
+/* gsmfret_c.h — C ABI of libgsmfret.so: the drop-in boundary of the B200-native
+ * Monte-Carlo PDA evaluation.
+ *
+ * The reference (liu-kan/gSMFRETda) has no C ABI; its boundary is the C++ class `mc`
+ * (/root/reference/src/mc.hpp:78-179) driven by gpuWorker::run
+ * (/root/reference/src/gpuWorker.cpp:71-80) and read by streamWorker::run
+ * (/root/reference/src/streamWorker.cpp:186-206).  Each entry point below replaces one
+ * member of that class (cited per function); gsmfretda_b200/host/mc.hpp re-creates the
+ * C++ class on top of this header, INTEGRATION.md shows the reference-side binding.
+ *
+ * Conventions: plain pointers and sizes only.  Functions returning `int` status return
+ * GSM_OK (0) or a negative GSM_E* code, with the text available from gsm_last_error()
+ * (thread-local).  The reference's convention — print "<stmt> returned <msg>(<code>) at
+ * file:line" and exit (/root/reference/src/cuda_tools.hpp:20-28) — is re-created by the C++
+ * shim, not here.  Input arrays stay owned by the caller and may be freed after the call
+ * returns; result pointers are library-owned pinned host memory, valid until the next
+ * gsm_run*() on the same stream slot or gsm_destroy().
+ *
+ * Threading contract (same as the reference): all calls that take a
+ * stream id `sid` come from one thread at a time per sid; results of slot `sid` may be
+ * read by another thread once gsm_query(ctx, sid) returned 1.
+ *
+ * There is no CPU fallback: every compute entry point needs a CUDA device of compute
+ * capability 10.0 (sm_100a) and fails with GSM_ENODEVICE otherwise.
+ */
+#ifndef GSMFRET_C_H
+#define GSMFRET_C_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSM_ABI_VERSION 1
+
+#define GSM_OK 0
+#define GSM_EINVAL (-1)    /* bad argument */
+#define GSM_ECUDA (-2)     /* a CUDA runtime call failed */
+#define GSM_ENODEVICE (-3) /* no usable sm_100 device */
+#define GSM_ESTATE (-4)    /* call out of order (e.g. run before init_data) */
+#define GSM_ENCCL (-5)     /* an NCCL call failed */
+#define GSM_ERANGE (-6)    /* input outside the draw contract (e.g. background lambda >= 1000) */
+
+/* gsm_create flags */
+#define GSM_KEEP_MCE 1u     /* also return the per-sample efficiencies (mc::hmcE) */
+#define GSM_KEEP_COUNTS 2u  /* also return per-sample integer acceptor counts and dwell steps */
+#define GSM_FORCE_RAW64 4u  /* do not pack photons: read burst_ad/burst_dd as uploaded */
+
+typedef struct gsm_ctx gsm_ctx;
+
+int gsm_abi_version(void);
+const char* gsm_last_error(void);
+/* number of CUDA devices of compute capability 10.x visible to the process */
+int gsm_device_count(void);
+
+/* mc::mc(devid, streamNum, debug, hdf5size, profiler)   mc.cu:212-324
+ * stream_num == 0 selects 2 x asyncEngineCount as the reference does (mc.cu:61-66,219-225). */
+int gsm_create(int devid, int stream_num, unsigned flags, gsm_ctx** out);
+/* mc::~mc()   mc.cu:618-660  (does NOT call cudaDeviceReset: the process may own other contexts) */
+void gsm_destroy(gsm_ctx* ctx);
+/* mc::set_gpuid()   mc.cu:199-211 : bind the calling thread to the context's device */
+int gsm_set_device(gsm_ctx* ctx);
+/* mc::getStreams(&n)   mc.cu:661-664 */
+int gsm_stream_count(const gsm_ctx* ctx);
+void* gsm_stream(const gsm_ctx* ctx, int sid); /* cudaStream_t */
+int gsm_device_id(const gsm_ctx* ctx);
+/* mc::gpuuuid : 32 hex digits + NUL */
+int gsm_device_uuid(const gsm_ctx* ctx, char out[33]);
+
+/* mc::set_reSampleTimes(n)   mc.cu:316-318 ; any R >= 1 (the reference needs a power of two) */
+int gsm_set_resample_times(gsm_ctx* ctx, int R);
+int gsm_resample_times(const gsm_ctx* ctx);
+/* key of the counter-based generator; the reference seeds from cuRAND tables (mc.cu:366-455) */
+int gsm_set_seed(gsm_ctx* ctx, uint32_t seed);
+/* fretHistNum / leftPad of streamWorker (streamWorker.cpp:41,62-70; main.cpp:155); defaults 200, 2 */
+int gsm_set_hist(gsm_ctx* ctx, int n_bins, int left_pad);
+
+/* mc::init_data_gpu(...)   mc.cu:456-521 : one-time upload of the burst arrays.
+ * g_offset is the global index of burst 0 when a dataset is split across GPUs (0 otherwise).
+ * Also builds the observed histogram of SgDivSr (streamWorker.cpp:62-70). */
+int gsm_init_data(gsm_ctx* ctx, int64_t n_bursts, const int64_t* istart, const int64_t* start,
+                  const int64_t* stop, const int32_t* ph_count, int64_t n_photons,
+                  const int64_t* burst_ad, const int64_t* burst_dd, const float* T,
+                  const float* SgDivSr, float clk_p, float bg_ad_rate, float bg_dd_rate,
+                  int64_t g_offset);
+/* mc::sz_burst */
+int64_t gsm_n_bursts(const gsm_ctx* ctx);
+/* 1 if the photons were packed to 4 bytes each, 0 if the raw int64 layout is in use */
+int gsm_is_packed(const gsm_ctx* ctx);
+/* observed histogram, n_bins floats (streamWorker's ohist) */
+int gsm_observed_hist(gsm_ctx* ctx, float* out, int n_bins);
+/* replace the observed histogram (burst-split runs hand every rank the global one) */
+int gsm_set_observed_hist(gsm_ctx* ctx, const float* ohist, int n_bins);
+
+/* mc::get_max_conversion_capacity()   mc.cu:326-365 : dead buffer grab in the reference; no-op, returns 1 */
+int gsm_get_max_conversion_capacity(gsm_ctx* ctx, int max_state_num);
+/* mc::set_nstates(n, sid) -> previous n   mc.cu:723-782 */
+int gsm_set_nstates(gsm_ctx* ctx, int n, int sid);
+/* mc::set_params(n, sid, args) -> 1, or 0 when n_args != n*n+n (eigenhelper.cpp:5-8)   mc.cu:790-829
+ * args = [E_0..E_{n-1} | k (n*n-n, row-major without the diagonal) | v_0..v_{n-1}] */
+int gsm_set_params(gsm_ctx* ctx, int n, int sid, const float* args, int n_args);
+/* mc::setBurstBd(cstart, cstop, sid) -> N (-1 if cstart == -1)   mc.cu:523-566
+ * As in the reference the evaluated bursts are [0, N): the range start is not applied (quirk Q7). */
+int gsm_set_burst_bd(gsm_ctx* ctx, int cstart, int cstop, int sid);
+/* mc::init_randstate(N, sid)   mc.cu:366-455 : nothing to allocate with a counter-based
+ * generator; starts a new draw epoch for the slot. */
+int gsm_init_randstate(gsm_ctx* ctx, int N, int sid);
+/* mc::set_params_buff(oldS_n, N_sid, sid)   mc.cu:783-789 : no scratch needed; no-op */
+int gsm_set_params_buff(gsm_ctx* ctx, int old_n, int N_sid, int sid);
+/* explicit draw epoch of the next run on the slot (replay); otherwise it advances by one per run */
+int gsm_set_epoch(gsm_ctx* ctx, int sid, uint32_t epoch);
+
+/* mc::run_kernel(N, sid)   mc.cu:567-617 : asynchronous; enqueues the evaluation of bursts
+ * [0, N) x R repeats with the slot's parameters and the copy of the results to pinned host
+ * memory on the slot's stream, and returns. */
+int gsm_run(gsm_ctx* ctx, int N, int sid);
+/* batch entry: P parameter vectors of n states in one launch (args = P rows of n*n+n floats);
+ * vector p draws with epoch + p.  Results via gsm_result_chi2v / gsm_result_histv. */
+int gsm_run_batch(gsm_ctx* ctx, int N, int sid, int n, int P, const float* args);
+/* same, the vectors of the previous gsm_run_batch / gsm_set_params stay resident: only launches */
+int gsm_run_resident(gsm_ctx* ctx, int N, int sid);
+/* mc::streamQuery(sid)   mc.cu:665-672 : 1 finished, 0 still running, <0 error */
+int gsm_query(gsm_ctx* ctx, int sid);
+int gsm_sync(gsm_ctx* ctx, int sid);
+
+/* results of the last run on the slot (valid after gsm_query == 1 / gsm_sync) */
+float gsm_result_chi2(const gsm_ctx* ctx, int sid);
+const float* gsm_result_chi2v(const gsm_ctx* ctx, int sid, int* P);
+/* histogram of vector p: n_bins inner counts, then [n_bins] overflow (E >= 1, NaN), [n_bins+1] underflow */
+const uint64_t* gsm_result_hist(const gsm_ctx* ctx, int sid, int p);
+/* mc::hmcE[sid] : N*R floats per vector (needs GSM_KEEP_MCE) */
+const float* gsm_result_mcE(const gsm_ctx* ctx, int sid);
+/* per-sample integer acceptor counts / dwell steps (need GSM_KEEP_COUNTS) */
+const int64_t* gsm_result_counts(const gsm_ctx* ctx, int sid);
+const int32_t* gsm_result_steps(const gsm_ctx* ctx, int sid);
+/* bit 0: a sample hit the dwell-step cap (2^20; rates <= 0 hang the reference) */
+uint64_t gsm_result_flags(const gsm_ctx* ctx, int sid);
+/* device time of the last run on the slot between its first and last enqueued operation, ms */
+float gsm_last_elapsed_ms(gsm_ctx* ctx, int sid);
+/* number of kernels this library launched on behalf of the context so far */
+uint64_t gsm_launch_count(const gsm_ctx* ctx);
+
+/* burst-split evaluation across GPUs (new capability): every rank holds a
+ * contiguous range of the bursts; each run all-reduces the [P x (n_bins+2)] histograms with
+ * NCCL over NVLink before chi-square is taken, so every rank reports the global result. */
+int gsm_comm_unique_id(void* out128);               /* ncclGetUniqueId, 128 bytes */
+int gsm_comm_init(gsm_ctx* ctx, const void* id128, int rank, int world);
+int gsm_comm_destroy(gsm_ctx* ctx);
+
+/* primitive probes: one element per input through the device code, for the unit tests
+ * (role of the reference's test kernels, /root/reference/tests/GenRandTest.cu:107-135,272-287).
+ * what: 0 philox, 1 logf, 2 log, 3 exp, 4 normal icdf, 5 sixth root, 6 u01, 7 binomial,
+ * 8 poisson, 9 drawE, 10 drawTau, 11 multinomial, 12 categorical, 13 histogram index. */
+int gsm_probe(gsm_ctx* ctx, int what, int64_t n, int ni, int nj, const uint32_t* w0,
+              const uint32_t* w1, const float* f0, const float* f1, const double* d0,
+              const int32_t* i0, uint32_t* ou, float* of, double* od, int64_t* ol, int32_t* oi);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
