@@ -17,6 +17,7 @@ LIB_PATH = os.path.join(_HERE, "libgsmfret.so")
 GSM_KEEP_MCE = 1
 GSM_KEEP_COUNTS = 2
 GSM_FORCE_RAW64 = 4
+GSM_NO_INDEX = 8
 
 _f32p = C.POINTER(C.c_float)
 _f64p = C.POINTER(C.c_double)
@@ -46,6 +47,7 @@ SIGNATURES = {
                                 _f32p, _f32p, C.c_float, C.c_float, C.c_float, C.c_int64]),
     "gsm_n_bursts": (C.c_int64, [_ctx]),
     "gsm_is_packed": (C.c_int, [_ctx]),
+    "gsm_layout": (C.c_int, [_ctx]),
     "gsm_observed_hist": (C.c_int, [_ctx, _f32p, C.c_int]),
     "gsm_set_observed_hist": (C.c_int, [_ctx, _f32p, C.c_int]),
     "gsm_get_max_conversion_capacity": (C.c_int, [_ctx, C.c_int]),
@@ -110,10 +112,10 @@ class Mc:
     Extra (fused path): `hist(sid, p)`, `chi2(sid)`; `hmcE(sid)` needs keep_mce=True."""
 
     def __init__(self, devid: int = 0, streamNum: int = 16, keep_mce: bool = False,
-                 keep_counts: bool = False, force_raw64: bool = False):
+                 keep_counts: bool = False, force_raw64: bool = False, no_index: bool = False):
         self.lib = load()
         flags = (GSM_KEEP_MCE if keep_mce else 0) | (GSM_KEEP_COUNTS if keep_counts else 0) | \
-                (GSM_FORCE_RAW64 if force_raw64 else 0)
+                (GSM_FORCE_RAW64 if force_raw64 else 0) | (GSM_NO_INDEX if no_index else 0)
         h = _ctx()
         self._h = None
         self._ck(self.lib.gsm_create(devid, streamNum, flags, C.byref(h)))
@@ -288,6 +290,9 @@ class Mc:
 
     def is_packed(self) -> bool:
         return bool(self.lib.gsm_is_packed(self._h))
+
+    def layout(self) -> int:
+        return int(self.lib.gsm_layout(self._h))
 
     def observed_hist(self) -> np.ndarray:
         out = np.zeros(self.n_bins, np.float32)

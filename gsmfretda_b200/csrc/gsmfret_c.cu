@@ -117,9 +117,12 @@ struct gsm_ctx {
     bool inited = false;
     int64_t B = 0, n_photons = 0, g_offset = 0;
     bool packed = false, with_bg = false;
+    int layout = 0;  // 0 raw int64 ticks, 1 packed words, 2 packed words + index
     float clk_p = 0, bg_ad = 0, bg_dd = 0;
     BurstRec* d_bursts = nullptr;
     int32_t* d_pk = nullptr;
+    int32_t* d_pm = nullptr;
+    uint32_t* d_nx = nullptr;
     int64_t* d_ad = nullptr; int64_t* d_dd = nullptr;
     float* d_sg = nullptr;
     float* d_ohist = nullptr;
@@ -343,7 +346,8 @@ void gsm_destroy(gsm_ctx* c)
         if (s.ev1) cudaEventDestroy(s.ev1);
         if (s.stream) cudaStreamDestroy(s.stream);
     }
-    cudaFree(c->d_bursts); cudaFree(c->d_pk); cudaFree(c->d_ad); cudaFree(c->d_dd);
+    cudaFree(c->d_bursts); cudaFree(c->d_pk); cudaFree(c->d_pm); cudaFree(c->d_nx);
+    cudaFree(c->d_ad); cudaFree(c->d_dd);
     cudaFree(c->d_sg); cudaFree(c->d_ohist);
     cudaGetLastError();
     delete c;
@@ -394,7 +398,10 @@ int gsm_set_hist(gsm_ctx* c, int n_bins, int left_pad)
             if (s.d_whist) CK(cudaMemset(s.d_whist, 0, s.cap_res));
             s.ran = false;
         }
-        if (c->inited) return build_observed(c);
+        if (c->inited) {
+            c->cfg = eval_launch_cfg(c->devid, c->layout, c->with_bg, c->nb);
+            return build_observed(c);
+        }
     }
     return GSM_OK;
 }
@@ -416,12 +423,14 @@ int gsm_init_data(gsm_ctx* c, int64_t B, const int64_t* istart, const int64_t* s
     std::vector<int64_t> poff((size_t)B);
     int64_t pk_total = 0;
     double max_lambda = 0.0;
+    int64_t max_ph = 0;
     for (int64_t b = 0; b < B; ++b) {
         const int64_t ph = ph_count[b];
         if (ph < 0 || istart[b] < 0 || istart[b] + ph > n_photons)
             return fail(GSM_EINVAL, "burst %lld: photons [%lld, %lld) outside [0, %lld)", (long long)b,
                         (long long)istart[b], (long long)(istart[b] + ph), (long long)n_photons);
         poff[b] = pk_total;
+        if (ph > max_ph) max_ph = ph;
         pk_total += (ph + 3) & ~(int64_t)3;
         if (with_bg) {
             double span = (double)(stop[b] - start[b]) * (double)clk_p;
@@ -433,8 +442,10 @@ int gsm_init_data(gsm_ctx* c, int64_t B, const int64_t* istart, const int64_t* s
         return fail(GSM_ERANGE, "background mean %g per burst: the Poisson draw contract covers lambda < 1000", max_lambda);
     CK(cudaSetDevice(c->devid));
     for (Slot& s : c->slots) CK(cudaStreamSynchronize(s.stream));
-    cudaFree(c->d_bursts); cudaFree(c->d_pk); cudaFree(c->d_ad); cudaFree(c->d_dd); cudaFree(c->d_sg);
-    c->d_bursts = nullptr; c->d_pk = nullptr; c->d_ad = nullptr; c->d_dd = nullptr; c->d_sg = nullptr;
+    cudaFree(c->d_bursts); cudaFree(c->d_pk); cudaFree(c->d_pm); cudaFree(c->d_nx);
+    cudaFree(c->d_ad); cudaFree(c->d_dd); cudaFree(c->d_sg);
+    c->d_bursts = nullptr; c->d_pk = nullptr; c->d_pm = nullptr; c->d_nx = nullptr;
+    c->d_ad = nullptr; c->d_dd = nullptr; c->d_sg = nullptr;
     c->inited = false;
 
     int64_t *d_start = nullptr, *d_stop = nullptr, *d_istart = nullptr, *d_poff = nullptr;
@@ -466,22 +477,33 @@ int gsm_init_data(gsm_ctx* c, int64_t B, const int64_t* istart, const int64_t* s
     }
     CKT(cudaMemset(d_bad, 0, 4));
     bool packed = !(c->flags & GSM_FORCE_RAW64);
-    PackArgs pa{d_start, d_stop, d_istart, d_ph, d_T, c->d_ad, c->d_dd, d_poff, c->d_bursts, nullptr, d_bad, B};
+    // the next-photon distances are 16-bit: longer bursts keep the photon-by-photon scan
+    bool indexed = packed && !(c->flags & GSM_NO_INDEX) && max_ph <= 65535;
+    PackArgs pa{};
+    pa.start = d_start; pa.stop = d_stop; pa.istart = d_istart; pa.ph = d_ph; pa.T = d_T;
+    pa.ad = c->d_ad; pa.dd = c->d_dd; pa.poff = d_poff; pa.bursts = c->d_bursts;
+    pa.bad = d_bad; pa.B = B;
     if (packed) {
-        CKT(cudaMalloc((void**)&c->d_pk, (size_t)(pk_total > 0 ? pk_total : 4) * 4));
+        const size_t words = (size_t)(pk_total > 0 ? pk_total : 4);
+        CKT(cudaMalloc((void**)&c->d_pk, words * 4));
         pa.pk = c->d_pk;
+        if (indexed) {
+            CKT(cudaMalloc((void**)&c->d_pm, words * 4));
+            CKT(cudaMalloc((void**)&c->d_nx, words * 4));
+            pa.pm = c->d_pm; pa.nx = c->d_nx;
+        }
         CKT(launch_pack(pa, 0));
-        c->launches += (B ? 1 : 0);
+        c->launches += (B ? (indexed ? 2 : 1) : 0);
         unsigned int bad = 0;
         CKT(cudaMemcpy(&bad, d_bad, 4, cudaMemcpyDeviceToHost));
         if (bad) {  // ticks too far from their burst start for 30 bits: keep the raw layout
-            packed = false;
-            cudaFree(c->d_pk);
-            c->d_pk = nullptr;
+            packed = false; indexed = false;
+            cudaFree(c->d_pk); cudaFree(c->d_pm); cudaFree(c->d_nx);
+            c->d_pk = nullptr; c->d_pm = nullptr; c->d_nx = nullptr;
         }
     }
     if (!packed) {
-        pa.pk = nullptr;
+        pa.pk = nullptr; pa.pm = nullptr; pa.nx = nullptr;
         CKT(launch_pack(pa, 0));
         c->launches += (B ? 1 : 0);
     } else {
@@ -493,8 +515,9 @@ int gsm_init_data(gsm_ctx* c, int64_t B, const int64_t* istart, const int64_t* s
     free_tmp();
     c->B = B; c->n_photons = n_photons; c->g_offset = g_offset;
     c->packed = packed; c->with_bg = with_bg;
+    c->layout = packed ? (indexed ? 2 : 1) : 0;
     c->clk_p = clk_p; c->bg_ad = bg_ad_rate; c->bg_dd = bg_dd_rate;
-    c->cfg = eval_launch_cfg(c->devid, packed, with_bg);
+    c->cfg = eval_launch_cfg(c->devid, c->layout, with_bg, c->nb);
     c->inited = true;
     for (Slot& s : c->slots) { s.N = -1; s.ran = false; }
     return build_observed(c);
@@ -502,6 +525,7 @@ int gsm_init_data(gsm_ctx* c, int64_t B, const int64_t* istart, const int64_t* s
 
 int64_t gsm_n_bursts(const gsm_ctx* c) { return c ? c->B : 0; }
 int gsm_is_packed(const gsm_ctx* c) { return c && c->packed ? 1 : 0; }
+int gsm_layout(const gsm_ctx* c) { return c ? c->layout : -1; }
 
 int gsm_observed_hist(gsm_ctx* c, float* out, int n_bins)
 {
@@ -601,7 +625,7 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
     if (r) return r;
     const int nbp = c->nb + 2;
     EvalArgs a{};
-    a.bursts = c->d_bursts; a.pk = c->d_pk; a.ad = c->d_ad; a.dd = c->d_dd;
+    a.bursts = c->d_bursts; a.pk = c->d_pk; a.pm = c->d_pm; a.nx = c->d_nx; a.ad = c->d_ad; a.dd = c->d_dd;
     a.params = s.d_params; a.ohist = c->d_ohist;
     a.whist = s.d_whist;
     a.hist_out = res_hist(s.d_res);
@@ -622,7 +646,7 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
         CK(cudaMemcpyAsync(s.d_params, s.h_params, (size_t)s.P * sizeof(ParamRaw), cudaMemcpyHostToDevice, s.stream));
         s.params_resident = true;
     }
-    CK(launch_eval(a, c->packed, c->with_bg, c->cfg, s.stream));
+    CK(launch_eval(a, c->layout, c->with_bg, c->cfg, s.stream));
     c->launches += 1;
     if (c->comm) {
         int e = g_nccl.AllReduce(s.d_whist, s.d_whist, (size_t)s.P * nbp, kNcclUint64, kNcclSum, c->comm, s.stream);

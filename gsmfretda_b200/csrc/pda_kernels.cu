@@ -6,11 +6,13 @@
 // the reference computes on the host after copying N*R floats back.
 //
 // Design:
-//  * persistent grid, one ticket counter hands out tiles of blockDim consecutive samples,
-//    so that lanes of a warp are repeats of the same / neighbouring bursts and read the
-//    same photon words (one L1 transaction per warp-wide load);
+//  * persistent grid of autonomous warps; one ticket counter hands out chunks of consecutive
+//    samples, a lane that finishes its sample takes the next one of the warp's chunk, so the
+//    warp stays converged on the expensive part whatever the window count per sample, and
+//    lanes of a warp are repeats of the same / neighbouring bursts (shared photon words);
 //  * photons are one packed 32-bit word each, (tick - burst start) << 2 | channel flags,
-//    instead of the reference's two int64 (16 B -> 4 B per photon);
+//    instead of the reference's two int64, plus a running-maximum word and a next-photon
+//    word per photon that turn the per-window photon scan into a binary search;
 //  * RNG is Philox4x32-10 keyed by (global burst, repeat, step, slot): no state in memory;
 //  * per-block shared-memory histogram with warp-aggregated atomics, one 64-bit global
 //    atomic per non-empty bin per block, and the last block to finish reduces chi-square,
@@ -21,6 +23,7 @@
 namespace pda {
 
 constexpr int kBlock = 256;
+constexpr int kChunk = 256;             // consecutive samples a warp draws per ticket
 constexpr int kMaxBins = 1024;          // nb + 2 <= kMaxBins
 constexpr uint32_t kStepCap = 1u << 20; // guards the GPU against rates <= 0 (a hang in the reference)
 
@@ -35,9 +38,9 @@ struct SmemParams {
     float cumP[kMaxStates];             // running sums of p
 };
 
-__device__ __forceinline__ void stage_params(SmemParams& sp, const ParamRaw* __restrict__ pr)
+// executed by one warp (tid = lane)
+__device__ __forceinline__ void stage_params(SmemParams& sp, const ParamRaw* __restrict__ pr, int tid)
 {
-    const int tid = threadIdx.x;
     const int n = pr->n;
     if (tid == 0) sp.n = n;
     if (tid < n) {
@@ -52,8 +55,8 @@ __device__ __forceinline__ void stage_params(SmemParams& sp, const ParamRaw* __r
             sp.cumJ[tid][ii] = a;
         }
     }
-    if (tid < n * n) sp.K[tid] = pr->K[tid];
-    if (tid == 32) {
+    for (int i = tid; i < n * n; i += 32) sp.K[i] = pr->K[i];
+    if (tid == 31) {
         float a = 0.0f;
         for (int i = 0; i < n; ++i) {
             a += pr->p[i];
@@ -71,122 +74,178 @@ __device__ __forceinline__ int pick(const float* cum, int m, float pv)
     return r;
 }
 
-struct SampleOut {
-    float mcE;
+// ------------------------------------------------------------------------------------
+// One lane carries one burst-sample at a time; every trip of the warp's main loop advances
+// each lane by ONE dwell window, and a lane whose sample is finished takes the next sample of
+// the warp's chunk.  Lanes therefore stay converged on the expensive part (Philox, the
+// draws, the FP64 binomial) whatever the number of windows of their samples.
+// ------------------------------------------------------------------------------------
+struct Lane {
+    // sample identity
+    int64_t t;          // sample index inside the parameter vector: burst_local * R + repeat
+    uint32_t g, rep;
+    // burst record
+    int64_t start, stop, off;
+    float T;
+    int ph;
+    // walk state
+    Xor128 xs;
+    float F, acc, spent;
     long long sum_ai;
-    uint32_t steps;
+    int64_t bin0;
+    int first, si;
+    uint32_t step;
 };
 
-template <bool kPacked, bool kBg>
-__device__ __forceinline__ SampleOut walk_sample(const SmemParams& sp, const EvalArgs& a,
-                                                 int64_t b, uint32_t g, uint32_t rep,
-                                                 uint32_t epoch)
+struct Window {
+    int end;        // index of the closing photon; >= ph: the window saw no photon at all
+    int f_ia, f_id; // counted acceptor / donor photons
+};
+
+// The reference's photon scan (/root/reference/src/mc.cu:140-181), photon by photon.
+template <bool kPacked>
+__device__ __forceinline__ Window scan_linear(const EvalArgs& a, const Lane& L, int64_t bin1, int thr)
 {
-    const int n = sp.n;
-    const int4 r0 = __ldg(reinterpret_cast<const int4*>(a.bursts + b));
-    const int4 r1 = __ldg(reinterpret_cast<const int4*>(a.bursts + b) + 1);
-    const int64_t start = ((int64_t)(uint32_t)r0.y << 32) | (uint32_t)r0.x;
-    const int64_t stop = ((int64_t)(uint32_t)r0.w << 32) | (uint32_t)r0.z;
-    const float T = __int_as_float(r1.x);
-    const int ph = r1.y;
-    const int64_t off = ((int64_t)(uint32_t)r1.w << 32) | (uint32_t)r1.z;
-    const int32_t* __restrict__ pk = kPacked ? a.pk + off : nullptr;
-    const int64_t* __restrict__ ad = kPacked ? nullptr : a.ad + off;
-    const int64_t* __restrict__ dd = kPacked ? nullptr : a.dd + off;
-    const float clk_p = a.clk_p;
-
-    Xor128 xs;
-    {
-        u32x4 sd = philox4x32_10(g, rep, 0u, kSlotSeed, a.seed, epoch);
-        xs.seed((uint64_t)sd.x | ((uint64_t)sd.y << 32));
-    }
-    u32x4 w = philox4x32_10(g, rep, 0u, kSlotStep, a.seed, epoch);
-
-    float F = 0.0f, acc = 0.0f, spent = 0.0f;
-    long long sum_ai = 0;
-    int si = pick(sp.cumP, n, u01(w.w));
-    int64_t bin0 = start, bin1 = start;
-    int first = 0;
-    uint32_t step = 0;
-    while (T > spent) {
-        if (step) w = philox4x32_10(g, rep, step, kSlotStep, a.seed, epoch);
-        int sj = pick(sp.cumJ[si], n - 1, u01(w.x));
-        if (sj >= si) ++sj;
-        float tau = det_logf(u01(w.y)) / (-sp.K[sj + si * n]);
-        spent = spent + tau;
-        if (spent >= T)
-            bin1 = stop;
-        else
-            bin1 = (int64_t)((float)bin0 + spent / clk_p);
-
-        int flags = 0, f_id = 0, f_ia = 0;
-        long long ai = 0;
-        int thr = 0;
+    Window w{L.ph, 0, 0};
+    int flags = 0;
+    for (int i = L.first; i < L.ph; ++i) {
+        bool close;
+        int fl;
         if (kPacked) {
-            // photon word w = rel*4 + flags compares against rel1*4; a window edge at or
-            // below tick 0 closes on any photon (0 >= bin1 holds for the empty channels too)
-            int64_t rel = bin1 - start;
-            rel = rel < -(1ll << 29) + 1 ? -(1ll << 29) + 1 : rel;
-            rel = rel > (1ll << 29) - 1 ? (1ll << 29) - 1 : rel;
-            thr = bin1 <= 0 ? INT32_MIN : (int)rel * 4;
+            int pw = __ldg(a.pk + L.off + i);
+            close = pw >= thr;
+            fl = pw & 3;
+        } else {
+            int64_t ddx = __ldg(a.dd + L.off + i), adx = __ldg(a.ad + L.off + i);
+            close = ddx >= bin1 || adx >= bin1;
+            fl = (ddx > 0 ? 1 : 0) | (adx > 0 ? 2 : 0);
         }
-        for (int i = first; i < ph; ++i) {
-            bool close;
-            int fl;
-            if (kPacked) {
-                int pw = __ldg(pk + i);
-                close = pw >= thr;
-                fl = pw & 3;
-            } else {
-                int64_t ddx = __ldg(dd + i), adx = __ldg(ad + i);
-                close = ddx >= bin1 || adx >= bin1;
-                fl = (ddx > 0 ? 1 : 0) | (adx > 0 ? 2 : 0);
-            }
-            if (close || i == ph - 1) {
-                first = i;
-                float f_if = (kGamma - kDch2Ach) * (float)f_id + (1.0f - kDexDirAem) * (float)f_ia;
-                float f_i;
-                F += f_if;
-                if (!kBg) {
-                    f_i = floorf(f_if + 0.5f);
-                } else {
-                    float t_diff = (float)(bin1 - bin0) * clk_p;
-                    float rf_ia = (1.0f - kDexDirAem) * (float)f_ia;
-                    u32x4 ba = philox4x32_10(g, rep, step, kSlotBgA, a.seed, epoch);
-                    uint32_t sv = poisson_itr(ba.x, ba.y, (double)(t_diff * a.bg_ad_rate));
-                    float bg_a = ((float)(int32_t)sv <= rf_ia) ? (float)(int32_t)sv
-                                                               : floorf(rf_ia * u01(ba.z));
-                    float rf_id = (kGamma - kDch2Ach) * (float)f_id;
-                    u32x4 bq = philox4x32_10(g, rep, step, kSlotBgD, a.seed, epoch);
-                    sv = poisson_itr(bq.x, bq.y, (double)(t_diff * a.bg_dd_rate));
-                    float bg_d = ((float)(int32_t)sv <= rf_id) ? (float)(int32_t)sv
-                                                               : floorf(rf_id * u01(bq.z));
-                    f_i = floorf(f_if - bg_d - bg_a + 0.5f);
-                }
-                float rd = det_norm_icdf(w.z) * sp.v[si] + sp.rootE[si];
-                float de = 1.0f / (1.0f + det_pow6f(rd / kR0));
-                ai = binomial(xs, (int)f_i, (double)de);
-                break;
-            }
-            flags |= fl;
-            if (flags == 3) continue;
-            f_ia += flags >> 1;
-            f_id += flags & 1;
-        }
-        acc += (float)ai;
-        sum_ai += ai;
-        bin0 = bin1;
-        si = sj;
-        if (++step >= kStepCap) {
-            atomicOr(a.counters + 2, 1ull);
+        if (close || i == L.ph - 1) {
+            w.end = i;
             break;
         }
+        flags |= fl;
+        if (flags == 3) continue;
+        w.f_ia += flags >> 1;
+        w.f_id += flags & 1;
     }
-    SampleOut o;
-    o.mcE = (F > 0.0f) ? acc / F : 0.0f;
-    o.sum_ai = sum_ai;
-    o.steps = step;
-    return o;
+    return w;
+}
+
+// Same result in O(log ph): the closing photon by binary search over the running maximum of
+// the photon words, the counts from the distance to the next acceptor / donor photon.
+// Exact whenever no photon before `first` already reaches the new edge; otherwise (a window
+// edge that moved backwards, unsorted ticks) the photon-by-photon scan decides.
+__device__ __forceinline__ Window scan_indexed(const EvalArgs& a, const Lane& L, int64_t bin1, int thr)
+{
+    if (L.first >= L.ph) return Window{L.ph, 0, 0};
+    const int32_t* __restrict__ pm = a.pm + L.off;
+    if (L.first > 0 && __ldg(pm + L.first - 1) >= thr) return scan_linear<true>(a, L, bin1, thr);
+    int lo = L.first, hi = L.ph - 1;  // the last photon closes any window that reaches it
+    while (lo < hi) {
+        int mid = (lo + hi) >> 1;
+        if (__ldg(pm + mid) >= thr) hi = mid;
+        else lo = mid + 1;
+    }
+    Window w{lo, 0, 0};
+    const uint32_t nx = __ldg(a.nx + L.off + L.first);
+    const int ia = L.first + (int)(nx & 0xffffu);  // next acceptor photon at or after `first`
+    const int id = L.first + (int)(nx >> 16);      // next donor photon
+    if (ia < id) {
+        int stop_at = id < lo ? id : lo;
+        w.f_ia = stop_at > ia ? stop_at - ia : 0;
+    } else if (id < ia) {
+        int stop_at = ia < lo ? ia : lo;
+        w.f_id = stop_at > id ? stop_at - id : 0;
+    }
+    return w;
+}
+
+// start a sample: burst record, binomial stream (role of setup_kernel, gen_rand.cuh:7-25)
+__device__ __forceinline__ void lane_begin(Lane& L, const EvalArgs& a, int64_t t, int64_t bl,
+                                           uint32_t rep, uint32_t epoch)
+{
+    const int64_t b = a.b0 + bl;
+    const int4 r0 = __ldg(reinterpret_cast<const int4*>(a.bursts + b));
+    const int4 r1 = __ldg(reinterpret_cast<const int4*>(a.bursts + b) + 1);
+    L.t = t;
+    L.g = (uint32_t)(b + a.g_offset);
+    L.rep = rep;
+    L.start = ((int64_t)(uint32_t)r0.y << 32) | (uint32_t)r0.x;
+    L.stop = ((int64_t)(uint32_t)r0.w << 32) | (uint32_t)r0.z;
+    L.T = __int_as_float(r1.x);
+    L.ph = r1.y;
+    L.off = ((int64_t)(uint32_t)r1.w << 32) | (uint32_t)r1.z;
+    u32x4 sd = philox4x32_10(L.g, rep, 0u, kSlotSeed, a.seed, epoch);
+    L.xs.seed((uint64_t)sd.x | ((uint64_t)sd.y << 32));
+    L.F = 0.0f; L.acc = 0.0f; L.spent = 0.0f;
+    L.sum_ai = 0;
+    L.bin0 = L.start;
+    L.first = 0;
+    L.si = 0;
+    L.step = 0;
+}
+
+// one dwell window (one trip of the reference's while loop, mc.cu:117-191)
+template <int kLayout, bool kBg>
+__device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const EvalArgs& a, uint32_t epoch)
+{
+    const int n = sp.n;
+    const u32x4 w = philox4x32_10(L.g, L.rep, L.step, kSlotStep, a.seed, epoch);
+    if (L.step == 0) L.si = pick(sp.cumP, n, u01(w.w));
+    const int si = L.si;
+    int sj = pick(sp.cumJ[si], n - 1, u01(w.x));
+    if (sj >= si) ++sj;
+    const float tau = det_logf(u01(w.y)) / (-sp.K[sj + si * n]);
+    L.spent = L.spent + tau;
+    int64_t bin1;
+    if (L.spent >= L.T)
+        bin1 = L.stop;
+    else
+        bin1 = (int64_t)((float)L.bin0 + L.spent / a.clk_p);
+
+    Window win;
+    if (kLayout == 0) {
+        win = scan_linear<false>(a, L, bin1, 0);
+    } else {
+        // photon word = rel*4 + flags compares against rel1*4; a window edge at or below
+        // tick 0 closes on any photon (0 >= bin1 holds for the empty channels too)
+        int64_t rel = bin1 - L.start;
+        rel = rel < -(1ll << 29) + 1 ? -(1ll << 29) + 1 : rel;
+        rel = rel > (1ll << 29) - 1 ? (1ll << 29) - 1 : rel;
+        const int thr = bin1 <= 0 ? INT32_MIN : (int)rel * 4;
+        win = (kLayout == 2) ? scan_indexed(a, L, bin1, thr) : scan_linear<true>(a, L, bin1, thr);
+    }
+
+    long long ai = 0;
+    if (win.end < L.ph) {
+        L.first = win.end;
+        const float f_if = (kGamma - kDch2Ach) * (float)win.f_id + (1.0f - kDexDirAem) * (float)win.f_ia;
+        float f_i;
+        L.F += f_if;
+        if (!kBg) {
+            f_i = floorf(f_if + 0.5f);
+        } else {
+            const float t_diff = (float)(bin1 - L.bin0) * a.clk_p;
+            const float rf_ia = (1.0f - kDexDirAem) * (float)win.f_ia;
+            const u32x4 ba = philox4x32_10(L.g, L.rep, L.step, kSlotBgA, a.seed, epoch);
+            uint32_t sv = poisson_itr(ba.x, ba.y, (double)(t_diff * a.bg_ad_rate));
+            const float bg_a = ((float)(int32_t)sv <= rf_ia) ? (float)(int32_t)sv : floorf(rf_ia * u01(ba.z));
+            const float rf_id = (kGamma - kDch2Ach) * (float)win.f_id;
+            const u32x4 bq = philox4x32_10(L.g, L.rep, L.step, kSlotBgD, a.seed, epoch);
+            sv = poisson_itr(bq.x, bq.y, (double)(t_diff * a.bg_dd_rate));
+            const float bg_d = ((float)(int32_t)sv <= rf_id) ? (float)(int32_t)sv : floorf(rf_id * u01(bq.z));
+            f_i = floorf(f_if - bg_d - bg_a + 0.5f);
+        }
+        const float rd = det_norm_icdf(w.z) * sp.v[si] + sp.rootE[si];
+        const float de = 1.0f / (1.0f + det_pow6f(rd / kR0));
+        ai = binomial(L.xs, (int)f_i, (double)de);
+    }
+    L.acc += (float)ai;
+    L.sum_ai += ai;
+    L.bin0 = bin1;
+    L.si = sj;
+    L.step++;
 }
 
 // reduced chi-square for parameter vector p, one thread, bins in the host loop's order
@@ -232,75 +291,162 @@ __device__ __forceinline__ void finalize_block(const EvalArgs& a)
     }
 }
 
-template <bool kPacked, bool kBg>
-__global__ void __launch_bounds__(kBlock) pda_eval_kernel(const EvalArgs a)
+// Persistent, warp-autonomous evaluation kernel.
+//   kLayout 0: raw int64 burst_ad/burst_dd (fallback), 1: packed words scanned photon by
+//   photon, 2: packed words + running-max / next-photon index (O(log ph) windows).
+// Every warp owns a copy of the parameter vector and a private histogram in shared memory,
+// draws chunks of kChunk consecutive samples from one global ticket, and only meets the other
+// warps of its block once, at the very end (last-block finalisation).
+template <int kLayout, bool kBg>
+__global__ void __launch_bounds__(kBlock, 2) pda_eval_kernel(const EvalArgs a)
 {
-    __shared__ SmemParams sp;
-    __shared__ unsigned int shist[kMaxBins];
-    __shared__ unsigned long long s_item;
+    constexpr int kWarps = kBlock / 32;
+    __shared__ SmemParams s_params[kWarps];
+    extern __shared__ unsigned int s_hist_all[];  // [kWarps][nbp]
     __shared__ int s_last;
 
-    const int tid = threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int wid = threadIdx.x >> 5;
+    const unsigned lt_mask = (1u << lane) - 1u;
     const int nbp = a.nb + 2;
-    const int64_t per_p = a.N * (int64_t)a.R;                      // samples per parameter vector
-    const unsigned long long tiles_per_p = (unsigned long long)((per_p + kBlock - 1) / kBlock);
-    const unsigned long long items = tiles_per_p * (unsigned long long)a.P;
+    SmemParams& sp = s_params[wid];
+    unsigned int* hist = s_hist_all + wid * nbp;
+
+    const int64_t per_p = a.N * (int64_t)a.R;  // samples per parameter vector
+    const unsigned long long chunks_per_p = (unsigned long long)((per_p + kChunk - 1) / kChunk);
+    const unsigned long long items = chunks_per_p * (unsigned long long)a.P;
     const bool small = per_p < (1ll << 31) && items < (1ull << 32);
 
-    for (int i = tid; i < nbp; i += kBlock) shist[i] = 0u;
-    int cur_p = -1;
+    for (int i = lane; i < nbp; i += 32) hist[i] = 0u;
+    __syncwarp();
+
+    int cur_p = -1;           // vector whose parameters / histogram this warp holds
+    uint32_t epoch = 0;
+    int64_t c_next = 0;       // next unassigned sample of the current chunk (index inside the vector)
+    int64_t c_end = 0;
+    bool have_pending = false;  // a fetched chunk of another vector waits for the lanes to drain
+    int pend_p = 0;
+    int64_t pend_next = 0, pend_end = 0;
+    bool exhausted = false;
+
+    Lane L;
+    bool active = false;
 
     for (;;) {
-        __syncthreads();  // s_item consumed by everyone, previous tile's histogram adds done
-        if (tid == 0) s_item = atomicAdd(a.counters + 0, 1ull);
-        __syncthreads();
-        const unsigned long long item = s_item;
-        if (item >= items) break;
-        const int p = small ? (int)((uint32_t)item / (uint32_t)tiles_per_p) : (int)(item / tiles_per_p);
-        const unsigned long long tile = item - (unsigned long long)p * tiles_per_p;
-        if (p != cur_p) {
-            if (cur_p >= 0) {  // flush the finished vector's bins
-                unsigned long long* gh = a.whist + (size_t)cur_p * nbp;
-                for (int i = tid; i < nbp; i += kBlock) {
-                    unsigned int c = shist[i];
-                    if (c) atomicAdd(gh + i, (unsigned long long)c);
-                    shist[i] = 0u;
+        // ---- hand samples to idle lanes -------------------------------------------------
+        for (;;) {
+            const unsigned need = __ballot_sync(0xffffffffu, !active);
+            if (need == 0u) break;
+            if (c_next >= c_end) {
+                if (have_pending) {
+                    if (need != 0xffffffffu) break;  // lanes of the previous vector still walking
+                    // all lanes idle: switch vector
+                    if (cur_p >= 0) {
+                        unsigned long long* gh = a.whist + (size_t)cur_p * nbp;
+                        for (int i = lane; i < nbp; i += 32) {
+                            unsigned int c = hist[i];
+                            if (c) atomicAdd(gh + i, (unsigned long long)c);
+                            hist[i] = 0u;
+                        }
+                    }
+                    __syncwarp();
+                    stage_params(sp, a.params + pend_p, lane);
+                    __syncwarp();
+                    cur_p = pend_p;
+                    epoch = a.epoch0 + (uint32_t)cur_p;
+                    c_next = pend_next;
+                    c_end = pend_end;
+                    have_pending = false;
+                    continue;
                 }
+                if (exhausted) break;
+                unsigned long long item = 0;
+                if (lane == 0) item = atomicAdd(a.counters + 0, 1ull);
+                item = __shfl_sync(0xffffffffu, item, 0);
+                if (item >= items) {
+                    exhausted = true;
+                    break;
+                }
+                const int p = small ? (int)((uint32_t)item / (uint32_t)chunks_per_p) : (int)(item / chunks_per_p);
+                const unsigned long long c = item - (unsigned long long)p * chunks_per_p;
+                const int64_t nx0 = (int64_t)c * kChunk;
+                const int64_t nx1 = nx0 + kChunk < per_p ? nx0 + kChunk : per_p;
+                if (p != cur_p) {
+                    have_pending = true;
+                    pend_p = p;
+                    pend_next = nx0;
+                    pend_end = nx1;
+                } else {
+                    c_next = nx0;
+                    c_end = nx1;
+                }
+                continue;
             }
-            stage_params(sp, a.params + p);
-            cur_p = p;
-            __syncthreads();
+            const int avail = (int)(c_end - c_next);
+            const int rank = __popc(need & lt_mask);
+            const bool take = !active && rank < avail;
+            const int want = __popc(need);
+            if (take) {
+                const int64_t t = c_next + rank;
+                const int64_t bl = small ? (int64_t)((uint32_t)t / (uint32_t)a.R) : t / a.R;
+                const uint32_t rep = (uint32_t)(t - bl * a.R);
+                lane_begin(L, a, t, bl, rep, epoch);
+                active = true;
+            }
+            c_next += want < avail ? want : avail;
+            // a burst of zero duration never enters the reference's while loop: E = 0
+            const bool dead = take && !(L.T > 0.0f);
+            if (dead) {
+                const size_t oi = (size_t)cur_p * (size_t)per_p + (size_t)L.t;
+                if (a.mcE) a.mcE[oi] = 0.0f;
+                if (a.sum_ai) a.sum_ai[oi] = 0;
+                if (a.n_steps) a.n_steps[oi] = 0;
+                atomicAdd(&hist[hist_index(0.0f, a.nb)], 1u);
+                active = false;
+            }
         }
-        const int64_t t = (int64_t)tile * kBlock + tid;
-        int bin = -1;
-        if (t < per_p) {
-            const int64_t bl = small ? (int64_t)((uint32_t)t / (uint32_t)a.R) : t / a.R;
-            const uint32_t rep = (uint32_t)(t - bl * a.R);
-            const int64_t b = a.b0 + bl;
-            SampleOut o = walk_sample<kPacked, kBg>(sp, a, b, (uint32_t)(b + a.g_offset), rep,
-                                                    a.epoch0 + (uint32_t)p);
-            const size_t oi = (size_t)p * (size_t)per_p + (size_t)t;
-            if (a.mcE) a.mcE[oi] = o.mcE;
-            if (a.sum_ai) a.sum_ai[oi] = o.sum_ai;
-            if (a.n_steps) a.n_steps[oi] = (int32_t)o.steps;
-            bin = hist_index(o.mcE, a.nb);
+        if (__ballot_sync(0xffffffffu, active) == 0u) {
+            if (exhausted && !have_pending) break;
+            continue;
+        }
+
+        // ---- one dwell window for every active lane -------------------------------------
+        if (active) {
+            lane_step<kLayout, kBg>(L, sp, a, epoch);
+            bool fin = !(L.T > L.spent);
+            if (!fin && L.step >= kStepCap) {
+                atomicOr(a.counters + 2, 1ull);
+                fin = true;
+            }
+            if (fin) {
+                const float e = (L.F > 0.0f) ? L.acc / L.F : 0.0f;
+                const size_t oi = (size_t)cur_p * (size_t)per_p + (size_t)L.t;
+                if (a.mcE) a.mcE[oi] = e;
+                if (a.sum_ai) a.sum_ai[oi] = L.sum_ai;
+                if (a.n_steps) a.n_steps[oi] = (int32_t)L.step;
+                // warp-aggregated add: one shared-memory atomic per distinct bin among the
+                // lanes that finish in this trip
+                const int bin = hist_index(e, a.nb);
+                const unsigned fm = __activemask();
+                const unsigned peers = __match_any_sync(fm, bin);
+                if (lane == __ffs(peers) - 1) atomicAdd(&hist[bin], (unsigned)__popc(peers));
+                active = false;
+            }
         }
         __syncwarp();
-        const unsigned peers = __match_any_sync(0xffffffffu, bin);
-        if (bin >= 0 && (tid & 31) == __ffs(peers) - 1) atomicAdd(&shist[bin], (unsigned)__popc(peers));
     }
 
-    // queue drained: flush, then the last block to arrive finalises
+    // queue drained: flush this warp's bins, then the last block to arrive finalises
     if (cur_p >= 0) {
         unsigned long long* gh = a.whist + (size_t)cur_p * nbp;
-        for (int i = tid; i < nbp; i += kBlock) {
-            unsigned int c = shist[i];
+        for (int i = lane; i < nbp; i += 32) {
+            unsigned int c = hist[i];
             if (c) atomicAdd(gh + i, (unsigned long long)c);
         }
     }
     __threadfence();
     __syncthreads();
-    if (tid == 0) {
+    if (threadIdx.x == 0) {
         unsigned long long done = atomicAdd(a.counters + 1, 1ull);
         s_last = (done == (unsigned long long)gridDim.x - 1ull);
     }
@@ -309,7 +455,7 @@ __global__ void __launch_bounds__(kBlock) pda_eval_kernel(const EvalArgs a)
         __threadfence();
         if (a.finalize) {
             finalize_block(a);
-        } else if (tid == 0) {
+        } else if (threadIdx.x == 0) {
             a.counters[0] = 0ull;
             a.counters[1] = 0ull;
         }
@@ -360,6 +506,31 @@ __global__ void pda_pack_kernel(const PackArgs a)
         a.pk[po + i] = word;
     }
     if (bad) atomicAdd(a.bad, bad);
+}
+
+// per-burst index over the packed words: running maximum (binary-searchable window edge) and
+// distance to the next acceptor / donor photon (window counts in O(1)); one thread per burst
+__global__ void pda_index_kernel(const PackArgs a)
+{
+    const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= a.B) return;
+    const int ph = a.ph[b];
+    const int64_t po = a.poff[b];
+    const int padded = (ph + 3) & ~3;
+    int m = INT32_MIN;
+    for (int i = 0; i < ph; ++i) {
+        const int key = a.pk[po + i] & ~3;
+        m = key > m ? key : m;
+        a.pm[po + i] = m;
+    }
+    for (int i = ph; i < padded; ++i) { a.pm[po + i] = INT32_MAX; a.nx[po + i] = 0u; }
+    int na = ph, nd = ph;
+    for (int i = ph - 1; i >= 0; --i) {
+        const int f = a.pk[po + i] & 3;
+        if (f & 2) na = i;
+        if (f & 1) nd = i;
+        a.nx[po + i] = (uint32_t)(na - i) | ((uint32_t)(nd - i) << 16);
+    }
 }
 
 // boost regular-axis histogram of a float array (observed SgDivSr histogram,
@@ -443,33 +614,37 @@ __global__ void pda_probe_kernel(const ProbeArgs a)
 // ------------------------------------------------------------------------------------
 // host-side launchers
 // ------------------------------------------------------------------------------------
-template <bool kPacked, bool kBg>
-static int resident_blocks()
+template <int kLayout, bool kBg>
+static int resident_blocks(size_t dyn)
 {
     int nb = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, pda_eval_kernel<kPacked, kBg>, kBlock, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, pda_eval_kernel<kLayout, kBg>, kBlock, dyn);
     return nb < 1 ? 1 : nb;
 }
 
-LaunchCfg eval_launch_cfg(int device, bool packed, bool with_bg)
+static size_t eval_dyn_smem(int nb) { return (size_t)(kBlock / 32) * (size_t)(nb + 2) * sizeof(unsigned int); }
+
+LaunchCfg eval_launch_cfg(int device, int layout, bool with_bg, int nb)
 {
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-    int per = packed ? (with_bg ? resident_blocks<true, true>() : resident_blocks<true, false>())
-                     : (with_bg ? resident_blocks<false, true>() : resident_blocks<false, false>());
+    const size_t dyn = eval_dyn_smem(nb);
+    int per;
+    if (layout == 0) per = with_bg ? resident_blocks<0, true>(dyn) : resident_blocks<0, false>(dyn);
+    else if (layout == 1) per = with_bg ? resident_blocks<1, true>(dyn) : resident_blocks<1, false>(dyn);
+    else per = with_bg ? resident_blocks<2, true>(dyn) : resident_blocks<2, false>(dyn);
     return LaunchCfg{sms * per, kBlock};
 }
 
-cudaError_t launch_eval(const EvalArgs& a, bool packed, bool with_bg, LaunchCfg cfg, cudaStream_t s)
+cudaError_t launch_eval(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s)
 {
     if (a.nb + 2 > kMaxBins) return cudaErrorInvalidValue;
-    if (packed) {
-        if (with_bg) pda_eval_kernel<true, true><<<cfg.grid, cfg.block, 0, s>>>(a);
-        else pda_eval_kernel<true, false><<<cfg.grid, cfg.block, 0, s>>>(a);
-    } else {
-        if (with_bg) pda_eval_kernel<false, true><<<cfg.grid, cfg.block, 0, s>>>(a);
-        else pda_eval_kernel<false, false><<<cfg.grid, cfg.block, 0, s>>>(a);
-    }
+    const size_t dyn = eval_dyn_smem(a.nb);
+#define PDA_LAUNCH(LAY, BG) pda_eval_kernel<LAY, BG><<<cfg.grid, cfg.block, dyn, s>>>(a)
+    if (layout == 0) { if (with_bg) PDA_LAUNCH(0, true); else PDA_LAUNCH(0, false); }
+    else if (layout == 1) { if (with_bg) PDA_LAUNCH(1, true); else PDA_LAUNCH(1, false); }
+    else { if (with_bg) PDA_LAUNCH(2, true); else PDA_LAUNCH(2, false); }
+#undef PDA_LAUNCH
     return cudaGetLastError();
 }
 
@@ -485,6 +660,7 @@ cudaError_t launch_pack(const PackArgs& a, cudaStream_t s)
     const int64_t threads = a.B * 32;
     const int64_t blocks = (threads + 255) / 256;
     pda_pack_kernel<<<(unsigned)blocks, 256, 0, s>>>(a);
+    if (a.pk && a.pm && a.nx) pda_index_kernel<<<(unsigned)((a.B + 127) / 128), 128, 0, s>>>(a);
     return cudaGetLastError();
 }
 

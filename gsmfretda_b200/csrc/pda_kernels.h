@@ -33,6 +33,8 @@ struct ParamRaw {
 struct EvalArgs {
     const BurstRec* bursts;
     const int32_t* pk;         // packed photons, (rel_tick << 2) | acceptor << 1 | donor ; or null
+    const int32_t* pm;         // running maximum of pk & ~3 inside each burst ; or null
+    const uint32_t* nx;        // distance to the next acceptor (low 16) / donor (high 16) photon ; or null
     const int64_t* ad;         // raw burst_ad / burst_dd (fallback layout); or null
     const int64_t* dd;
     const ParamRaw* params;    // [P]
@@ -64,8 +66,9 @@ struct LaunchCfg {
 };
 
 // how many blocks to launch (persistent grid: SMs x resident blocks)
-LaunchCfg eval_launch_cfg(int device, bool packed, bool with_bg);
-cudaError_t launch_eval(const EvalArgs& a, bool packed, bool with_bg, LaunchCfg cfg, cudaStream_t s);
+// layout: 0 raw int64 ticks, 1 packed words scanned linearly, 2 packed words + index
+LaunchCfg eval_launch_cfg(int device, int layout, bool with_bg, int nb);
+cudaError_t launch_eval(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s);
 // chi2 + copy-out + reset of the working histogram (used after a cross-GPU reduction)
 cudaError_t launch_finalize(const EvalArgs& a, cudaStream_t s);
 
@@ -76,6 +79,8 @@ struct PackArgs {
     const int64_t* poff;     // [B] packed offset of each burst (multiple of 4)
     BurstRec* bursts;        // out
     int32_t* pk;             // out, may be null (raw layout: bursts only)
+    int32_t* pm;             // out, may be null (no index)
+    uint32_t* nx;            // out, may be null
     unsigned int* bad;       // out: number of photons that do not fit the packed layout
     int64_t B;
 };

@@ -45,6 +45,7 @@ extern "C" {
 #define GSM_KEEP_MCE 1u     /* also return the per-sample efficiencies (mc::hmcE) */
 #define GSM_KEEP_COUNTS 2u  /* also return per-sample integer acceptor counts and dwell steps */
 #define GSM_FORCE_RAW64 4u  /* do not pack photons: read burst_ad/burst_dd as uploaded */
+#define GSM_NO_INDEX 8u     /* packed photons without the window index: photon-by-photon scan */
 
 typedef struct gsm_ctx gsm_ctx;
 
@@ -87,6 +88,9 @@ int gsm_init_data(gsm_ctx* ctx, int64_t n_bursts, const int64_t* istart, const i
 int64_t gsm_n_bursts(const gsm_ctx* ctx);
 /* 1 if the photons were packed to 4 bytes each, 0 if the raw int64 layout is in use */
 int gsm_is_packed(const gsm_ctx* ctx);
+/* photon layout in HBM: 0 raw int64 ticks (16 B/photon), 1 packed words (4 B/photon),
+ * 2 packed words + running-maximum + next-photon words (12 B/photon, O(log n) windows) */
+int gsm_layout(const gsm_ctx* ctx);
 /* observed histogram, n_bins floats (streamWorker's ohist) */
 int gsm_observed_hist(gsm_ctx* ctx, float* out, int n_bins);
 /* replace the observed histogram (burst-split runs hand every rank the global one) */

@@ -21,7 +21,7 @@ def run_gpu(gsm, b, n, args, R, seed, epoch, N=None, **kw):
         Ns = b.n_bursts if N is None else N
         tot = Ns * R
         return dict(chi2=chi2, hist=hist, mcE=mc.hmcE(0, tot), sum_ai=mc.counts(0, tot),
-                    n_steps=mc.steps(0, tot), packed=mc.is_packed(), flags=mc.flags(0),
+                    n_steps=mc.steps(0, tot), packed=mc.is_packed(), layout=mc.layout(), flags=mc.flags(0),
                     ohist=mc.observed_hist())
 
 
@@ -49,14 +49,21 @@ def check(gsm, oracle, b, n, args, R, seed=11, epoch=3, N=None, **kw):
 def test_configs_bit_exact(gsm, oracle, cfg, nb, R):
     w = synth.workload(cfg, n_bursts=nb, R=R)
     g = check(gsm, oracle, w.bursts(), w.n_states, w.args[0], R)
-    assert g["packed"]
+    assert g["packed"] and g["layout"] == 2
+
+
+@pytest.mark.parametrize("cfg,nb,R", [(1, 1000, 4), (2, 1500, 100), (3, 2000, 16), (5, 2000, 4)])
+def test_packed_linear_scan_bit_exact(gsm, oracle, cfg, nb, R):
+    w = synth.workload(cfg, n_bursts=nb, R=R)
+    g = check(gsm, oracle, w.bursts(), w.n_states, w.args[0], R, no_index=True)
+    assert g["layout"] == 1
 
 
 @pytest.mark.parametrize("cfg", [2, 5])
 def test_raw64_layout_bit_exact(gsm, oracle, cfg):
     w = synth.workload(cfg, n_bursts=1500, R=8)
     g = check(gsm, oracle, w.bursts(), w.n_states, w.args[0], 8, force_raw64=True)
-    assert not g["packed"]
+    assert not g["packed"] and g["layout"] == 0
 
 
 def test_partial_range(gsm, oracle):
