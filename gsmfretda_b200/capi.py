@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgsmfret.so")
+LIB_PATH = os.environ.get("GSMFRET_LIB") or os.path.join(_HERE, "libgsmfret.so")
 
 GSM_KEEP_MCE = 1
 GSM_KEEP_COUNTS = 2

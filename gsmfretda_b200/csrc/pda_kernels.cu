@@ -297,8 +297,11 @@ __device__ __forceinline__ void finalize_block(const EvalArgs& a)
 // Every warp owns a copy of the parameter vector and a private histogram in shared memory,
 // draws chunks of kChunk consecutive samples from one global ticket, and only meets the other
 // warps of its block once, at the very end (last-block finalisation).
+#ifndef PDA_MIN_BLOCKS
+#define PDA_MIN_BLOCKS 4
+#endif
 template <int kLayout, bool kBg>
-__global__ void __launch_bounds__(kBlock, 2) pda_eval_kernel(const EvalArgs a)
+__global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const EvalArgs a)
 {
     constexpr int kWarps = kBlock / 32;
     __shared__ SmemParams s_params[kWarps];
