@@ -1,0 +1,258 @@
+"""GPU: device primitives against the oracle bit for bit, the batch / resident / multi-stream
+entry points, edge cases, error behaviour, and full-size property checks."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from gsmfretda_b200 import synth
+from helpers import NB, LEFT_PAD, bits
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def mc1(gsm):
+    m = gsm.Mc(0, 1)
+    yield m
+    m.close()
+
+
+def test_probe_philox_and_math_bit_exact(mc1, oracle):
+    rng = np.random.default_rng(1)
+    n = 4096
+    ctr = rng.integers(0, 2 ** 32, 4 * n, dtype=np.uint64).astype(np.uint32)
+    key = rng.integers(0, 2 ** 32, 2 * n, dtype=np.uint64).astype(np.uint32)
+    got = mc1.probe(0, n, w0=ctr, w1=key, out="ou", out_len=4 * n)
+    L = oracle.lib
+    want = np.zeros(4 * n, np.uint32)
+    for i in range(n):
+        c = (C.c_uint32 * 4)(*[int(v) for v in ctr[4 * i:4 * i + 4]]); k = (C.c_uint32 * 2)(*[int(v) for v in key[2 * i:2 * i + 2]])
+        o = (C.c_uint32 * 4)()
+        L.pda_oracle_philox(c, k, o)
+        want[4 * i:4 * i + 4] = list(o)
+    assert np.array_equal(got, want)
+    kat = mc1.probe(0, 1, w0=np.zeros(4, np.uint32), w1=np.zeros(2, np.uint32), out="ou", out_len=4)
+    assert [int(v) for v in kat] == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+
+    w = rng.integers(0, 2 ** 32, n, dtype=np.uint64).astype(np.uint32)
+    w[:6] = [0, 1, 0x7fffffff, 0x80000000, 0x80000001, 0xffffffff]
+    assert np.array_equal(bits(mc1.probe(6, n, w0=w, out="of")), bits([L.pda_oracle_u01(int(v)) for v in w]))
+    assert np.array_equal(bits(mc1.probe(4, n, w0=w, out="of")), bits([L.pda_oracle_norm_icdf(int(v)) for v in w]))
+    x = (rng.random(n) ** 3 * 10 + 1e-12).astype(np.float32)
+    assert np.array_equal(bits(mc1.probe(1, n, f0=x, out="of")), bits([L.pda_oracle_logf(float(v)) for v in x]))
+    assert np.array_equal(bits(mc1.probe(5, n, f0=x, out="of")), bits([L.pda_oracle_root6f(float(v)) for v in x]))
+    d = rng.random(n) ** 4 + 1e-300
+    assert np.array_equal(mc1.probe(2, n, d0=d, out="od").view(np.uint64),
+                          np.array([L.pda_oracle_log(float(v)) for v in d]).view(np.uint64))
+    e = rng.uniform(-700, 700, n)
+    e[:3] = [0.0, -0.0, -500.0]
+    assert np.array_equal(mc1.probe(3, n, d0=e, out="od").view(np.uint64),
+                          np.array([L.pda_oracle_exp(float(v)) for v in e]).view(np.uint64))
+    k = (rng.random(n) * 5000 + 1e-3).astype(np.float32)
+    assert np.array_equal(bits(mc1.probe(10, n, w0=w, f0=k, out="of")),
+                          bits([L.pda_oracle_draw_tau(float(a), int(b)) for a, b in zip(k, w)]))
+    E = rng.uniform(0.02, 0.98, n).astype(np.float32); v = rng.uniform(0, 6, n).astype(np.float32)
+    assert np.array_equal(bits(mc1.probe(9, n, w0=w, f0=E, f1=v, out="of")),
+                          bits([L.pda_oracle_draw_e(float(a), 52.0, float(b), int(c)) for a, b, c in zip(E, v, w)]))
+    hx = np.concatenate([rng.uniform(-0.2, 1.2, n - 4), [1.0, np.nan, 0.0, -0.0]]).astype(np.float32)
+    hi = mc1.probe(13, n, ni=NB, f0=hx, out="oi")
+    want_h = np.zeros(NB + 2, np.uint64)
+    np.add.at(want_h, hi, 1)
+    assert np.array_equal(want_h, oracle.hist(hx, NB))
+
+
+def test_probe_binomial_poisson_bit_exact(mc1, oracle):
+    rng = np.random.default_rng(2)
+    L = oracle.lib
+    n = 3000
+    seeds = rng.integers(1, 2 ** 63, n).astype(np.uint64)
+    w = np.stack([(seeds & 0xffffffff).astype(np.uint32), (seeds >> 32).astype(np.uint32)], 1).reshape(-1)
+    nn = rng.choice([-3, -1, 0, 1, 2, 3, 5, 9, 20, 70, 150, 400, 3000], n).astype(np.int32)
+    pp = rng.choice([1e-3, 0.05, 0.3, 0.5, 0.62, 0.9, 0.999], n)
+    got = mc1.probe(7, n, ni=4, w0=w, i0=nn, d0=pp, out="ol")
+    st = (C.c_uint32 * 4)()
+    want = np.zeros(n, np.int64)
+    for i in range(n):
+        L.pda_oracle_rk_seed(int(seeds[i]), st)
+        s = 0
+        for _ in range(4):
+            s = (s * 31 + L.pda_oracle_binomial(st, int(nn[i]), float(pp[i])))
+            s = (s + 2 ** 63) % 2 ** 64 - 2 ** 63          # int64 wrap like the device
+        want[i] = s
+    assert np.array_equal(got, want)
+    lam = rng.choice([1e-4, 0.02, 0.7, 3.0, 40.0, 480.0, 510.0, 990.0], n)
+    got = mc1.probe(8, n, w0=w, d0=lam, out="ou")
+    want = np.array([L.pda_oracle_poisson(int(w[2 * i]), int(w[2 * i + 1]), float(lam[i])) for i in range(n)], np.uint32)
+    assert np.array_equal(got, want)
+
+
+def test_batch_matches_single_evaluations(gsm, oracle):
+    w = synth.workload(4, n_bursts=700, R=8, P=12)
+    b = w.bursts()
+    with gsm.Mc(0, 2, keep_mce=True) as mc:
+        mc.set_reSampleTimes(8); mc.set_seed(5); mc.set_hist(NB, LEFT_PAD)
+        mc.init_bursts(b)
+        mc.set_epoch(1, 40)
+        mc.run_batch(b.n_bursts, 1, 2, w.args)
+        mc.sync(1)
+        chi = mc.chi2v(1)
+        assert chi.shape == (12,)
+        mcE = mc.hmcE(1, 12 * b.n_bursts * 8).reshape(12, -1)
+        ohist = oracle.observed_hist(b, NB)
+        for p in range(12):
+            o = oracle.eval(b, 2, w.args[p], 8, 5, 40 + p)
+            assert np.array_equal(bits(mcE[p]), bits(o["mcE"]))
+            oh = oracle.hist(o["mcE"], NB)
+            assert np.array_equal(mc.hist(1, p), oh)
+            assert np.float32(chi[p]) == np.float32(oracle.chi2(ohist, oh, NB, 8, LEFT_PAD, 2))
+        # resident re-run: epoch advanced by P
+        mc.run_resident(b.n_bursts, 1); mc.sync(1)
+        o = oracle.eval(b, 2, w.args[3], 8, 5, 52 + 3)
+        assert np.array_equal(mc.hist(1, 3), oracle.hist(o["mcE"], NB))
+
+
+def test_streams_are_independent_and_async(gsm, oracle):
+    w2 = synth.workload(2, n_bursts=1500, R=16)
+    w3 = synth.workload(3, n_bursts=1500, R=16)
+    b = w3.bursts()
+    with gsm.Mc(0, 3) as mc:
+        assert mc.streamNum == 3 and len(set(mc.getStreams())) == 3
+        assert len(mc.gpuuuid) == 32
+        mc.set_reSampleTimes(16); mc.set_seed(9); mc.set_hist(NB, LEFT_PAD)
+        mc.init_bursts(b)
+        for sid, (n, a) in enumerate([(2, w2.args[0]), (3, w3.args[0]), (2, w2.args[0])]):
+            old = mc.set_nstates(n, sid)
+            assert old == 0
+            assert mc.set_params(n, sid, a)
+            N = mc.setBurstBd(0, -1, sid)
+            assert N == b.n_bursts
+            mc.init_randstate(N, sid); mc.set_params_buff(old, N, sid)
+            mc.set_epoch(sid, 100 + sid)
+            mc.run_kernel(N, sid)
+        for sid in range(3):
+            while not mc.streamQuery(sid):
+                pass
+        for sid, (n, a) in enumerate([(2, w2.args[0]), (3, w3.args[0]), (2, w2.args[0])]):
+            o = oracle.eval(b, n, a, 16, 9, 100 + sid)
+            assert np.array_equal(mc.hist(sid, 0), oracle.hist(o["mcE"], NB))
+        assert mc.set_nstates(3, 0) == 2           # previous n is returned
+        assert not mc.streamQuery(7)               # out of range -> false, as mc::streamQuery
+
+
+def test_setBurstBd_semantics(gsm):
+    b = synth.workload(1, n_bursts=100).bursts()
+    with gsm.Mc(0, 1) as mc:
+        mc.init_bursts(b)
+        assert mc.setBurstBd(0, -1, 0) == 100      # cstop < 0 -> sz_burst
+        assert mc.setBurstBd(0, 1000, 0) == 100    # cstop >= sz_burst -> sz_burst
+        assert mc.setBurstBd(10, 60, 0) == 50
+        assert mc.setBurstBd(70, 60, 0) == 60      # cstart >= cstop -> start 0
+        assert mc.setBurstBd(-1, 60, 0) == -1      # cstart == -1 -> N = -1
+
+
+def test_edge_datasets(gsm, oracle):
+    # empty dataset
+    e = synth.make_bursts(0, (0.5,), 1)
+    with gsm.Mc(0, 1) as mc:
+        mc.set_hist(NB, LEFT_PAD)
+        mc.init_bursts(e)
+        chi2, hist = mc.evaluate(2, synth.pack_args([0.3, 0.7], [10, 10], [1, 1]))
+        assert hist.sum() == 0
+    # a burst starting at tick 0, photon-less bursts, zero durations, one burst only
+    b = synth.make_bursts(40, (0.2, 0.8), 3, first_start=0)
+    b.ph_count[[0, 5, 39]] = 0
+    b.T[[2, 7]] = 0.0
+    args = synth.pack_args([0.2, 0.8], [300, 700], [2, 2])
+    for kw in ({}, dict(no_index=True), dict(force_raw64=True)):
+        with gsm.Mc(0, 1, keep_mce=True, keep_counts=True, **kw) as mc:
+            mc.set_reSampleTimes(5); mc.set_seed(1); mc.set_hist(NB, LEFT_PAD)
+            mc.init_bursts(b)
+            chi2, hist = mc.evaluate(2, args, epoch=2)
+            o = oracle.eval(b, 2, args, 5, 1, 2)
+            assert np.array_equal(bits(mc.hmcE(0, 200)), bits(o["mcE"]))
+            assert np.array_equal(mc.steps(0, 200), o["n_steps"])
+            assert np.array_equal(hist, oracle.hist(o["mcE"], NB))
+
+
+def test_unpackable_ticks_fall_back_to_raw64(gsm, oracle):
+    b = synth.make_bursts(50, (0.4,), 5)
+    b.stop = b.stop + (1 << 31)                       # a 2^31-tick burst does not fit 30 bits
+    last = b.istart + b.ph_count - 1
+    b.burst_dd[last] = b.stop - 1
+    b.burst_ad[last] = 0
+    args = synth.pack_args([0.4, 0.6], [200, 200], [2, 2])
+    with gsm.Mc(0, 1, keep_mce=True) as mc:
+        mc.set_reSampleTimes(4); mc.set_seed(2); mc.set_hist(NB, LEFT_PAD)
+        mc.init_bursts(b)
+        assert mc.layout() == 0
+        mc.evaluate(2, args, epoch=1)
+        o = oracle.eval(b, 2, args, 4, 2, 1)
+        assert np.array_equal(bits(mc.hmcE(0, 200)), bits(o["mcE"]))
+
+
+def test_errors(gsm):
+    b = synth.workload(1, n_bursts=50).bursts()
+    with gsm.Mc(0, 1) as mc:
+        with pytest.raises(gsm.GsmError):
+            mc.run_kernel(10, 0)                        # before init_data
+        mc.init_bursts(b)
+        assert mc.set_params(2, 0, [0.3, 0.7, 1.0, 1.0, 2.0]) is False      # wrong count -> false
+        assert mc.set_params(1, 0, [0.3, 2.0]) is False
+        with pytest.raises(gsm.GsmError):
+            mc.set_nstates(2, 5)                        # bad stream id
+        with pytest.raises(gsm.GsmError):
+            mc.hmcE(0, 10)                              # not kept
+        bad = synth.workload(5, n_bursts=20).bursts()
+        bad.bg_dd_rate = np.float32(5e6)                # lambda >= 1000: outside the Poisson contract
+        with pytest.raises(gsm.GsmError):
+            mc.init_bursts(bad)
+        bad2 = synth.workload(1, n_bursts=20).bursts()
+        bad2.istart = bad2.istart + 10 ** 9
+        with pytest.raises(gsm.GsmError):
+            mc.init_bursts(bad2)
+    with pytest.raises(gsm.GsmError):
+        gsm.Mc(99, 1)
+
+
+def test_step_cap_flags_nonpositive_rates(gsm):
+    b = synth.workload(1, n_bursts=64).bursts()
+    with gsm.Mc(0, 1) as mc:
+        mc.set_reSampleTimes(1); mc.set_hist(NB, LEFT_PAD)
+        mc.init_bursts(b)
+        mc.evaluate(2, synth.pack_args([0.3, 0.7], [-5.0, -5.0], [1, 1]))   # dwell times < 0: never ends
+        assert mc.flags(0) & 1
+
+
+@pytest.mark.parametrize("cfg", [2, 3, 5])
+def test_full_size_properties(gsm, oracle, cfg):
+    """BASELINE.json sizes (config 5 at 1e6 bursts: the generator, not the GPU, is the limit):
+    histogram mass, determinism, epoch sensitivity, additivity over burst ranges, and a
+    sampled bit-exact check of the first 2000 bursts against the oracle."""
+    w = synth.workload(cfg, n_bursts=1_000_000 if cfg == 5 else None)
+    b = w.bursts()
+    B, R, n = b.n_bursts, w.R, w.n_states
+    with gsm.Mc(0, 2) as mc:
+        mc.set_reSampleTimes(R); mc.set_seed(77); mc.set_hist(NB, LEFT_PAD)
+        mc.init_bursts(b)
+        assert mc.layout() == 2
+        c1, h1 = mc.evaluate(n, w.args[0], sid=0, epoch=5)
+        c2, h2 = mc.evaluate(n, w.args[0], sid=1, epoch=5)
+        c3, h3 = mc.evaluate(n, w.args[0], sid=0, epoch=6)
+        assert int(h1.sum()) == B * R
+        assert np.array_equal(h1, h2) and c1 == c2               # idempotent, stream-independent
+        assert not np.array_equal(h1, h3)                         # a new epoch draws anew
+        l1 = np.abs(h1.astype(np.int64) - h3.astype(np.int64)).sum() / (B * R)
+        assert l1 < 0.02 and abs(c3 / c1 - 1) < 0.25               # ... from the same distribution
+        _, ha = mc.evaluate(n, w.args[0], sid=0, N=2000, epoch=5)
+        o = oracle.eval(b, n, w.args[0], R, 77, 5, 0, 2000)
+        assert np.array_equal(ha, oracle.hist(o["mcE"], NB))
+    # additivity: two contexts holding the two halves with global burst ids sum to the whole
+    half = B // 2
+    hs = np.zeros(NB + 2, np.uint64)
+    for (b0, b1) in ((0, half), (half, B)):
+        with gsm.Mc(0, 1) as mc:
+            mc.set_reSampleTimes(R); mc.set_seed(77); mc.set_hist(NB, LEFT_PAD)
+            mc.init_bursts(b.slice(b0, b1), g_offset=b0)
+            hs += mc.evaluate(n, w.args[0], epoch=5)[1]
+    assert np.array_equal(hs, h1)

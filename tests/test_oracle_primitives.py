@@ -1,0 +1,130 @@
+"""The oracle's building blocks against published / independent answers (CPU only)."""
+import math
+
+import numpy as np
+import pytest
+
+from helpers import bits
+
+
+def philox(oracle, ctr, key):
+    import ctypes as C
+    c = (C.c_uint32 * 4)(*ctr); k = (C.c_uint32 * 2)(*key); o = (C.c_uint32 * 4)()
+    oracle.lib.pda_oracle_philox(c, k, o)
+    return [int(x) for x in o]
+
+
+def test_philox4x32_10_known_answers(oracle):
+    # Random123 kat_vectors, philox4x32 10 rounds
+    assert philox(oracle, [0, 0, 0, 0], [0, 0]) == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+    assert philox(oracle, [0xffffffff] * 4, [0xffffffff] * 2) == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
+    assert philox(oracle, [0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0]) == \
+        [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]
+
+
+def test_philox_matches_numpy_generator(oracle):
+    # numpy's Philox is philox4x64; no direct comparison.  Check instead the bijection
+    # property on a few counters: distinct counters -> distinct outputs, key sensitivity.
+    outs = {tuple(philox(oracle, [i, 0, 0, 0], [1, 2])) for i in range(2000)}
+    assert len(outs) == 2000
+    assert philox(oracle, [5, 6, 7, 8], [1, 2]) != philox(oracle, [5, 6, 7, 8], [1, 3])
+
+
+def test_u01_is_curand_mapping(oracle):
+    L = oracle.lib
+    assert L.pda_oracle_u01(0) == np.float32(2.0 ** -33)
+    assert L.pda_oracle_u01(0xffffffff) == np.float32(1.0)
+    assert 0.0 < L.pda_oracle_u01(1) < 1e-9
+
+
+def test_det_logf_accuracy(oracle):
+    rng = np.random.default_rng(1)
+    x = np.concatenate([rng.uniform(1e-10, 1.0, 20000), rng.uniform(1.0, 1e6, 2000)]).astype(np.float32)
+    got = np.array([oracle.lib.pda_oracle_logf(float(v)) for v in x], np.float32)
+    ref = np.log(x.astype(np.float64))
+    ulp = np.spacing(np.abs(ref).astype(np.float32)).astype(np.float64)
+    assert np.max(np.abs(got - ref) / np.maximum(ulp, 1e-45)) <= 1.5
+
+
+def test_det_log_exp_accuracy(oracle):
+    rng = np.random.default_rng(2)
+    x = rng.uniform(1e-300, 1.0, 5000) ** rng.uniform(0.1, 3, 5000)
+    x = np.concatenate([x, rng.uniform(1, 1e9, 1000)])
+    got = np.array([oracle.lib.pda_oracle_log(float(v)) for v in x])
+    ref = np.log(x)
+    assert np.max(np.abs(got - ref) / np.spacing(np.abs(ref))) <= 2.0
+    y = rng.uniform(-700, 700, 5000)
+    got = np.array([oracle.lib.pda_oracle_exp(float(v)) for v in y])
+    ref = np.exp(y)
+    assert np.max(np.abs(got - ref) / np.spacing(ref)) <= 2.0
+    assert oracle.lib.pda_oracle_exp(0.0) == 1.0 and oracle.lib.pda_oracle_exp(-0.0) == 1.0
+
+
+def test_det_norm_icdf_accuracy(oracle):
+    from scipy import special
+    rng = np.random.default_rng(3)
+    w = rng.integers(0, 2 ** 32, 20000, dtype=np.uint64).astype(np.uint32)
+    w = np.concatenate([w, np.array([0, 1, 2, 0x7fffffff, 0x80000000, 0x80000001, 0xfffffffe, 0xffffffff], np.uint32)])
+    got = np.array([oracle.lib.pda_oracle_norm_icdf(int(v)) for v in w], np.float64)
+    # cuRAND's mirrored mapping: p in (0, .5], z = +-sqrt(2) erfcinv(2p)
+    t = w.astype(np.float64)
+    neg = t > 2 ** 31
+    t = np.where(neg, 0xffffffff - t, t)
+    p = t * 2.0 ** -32 + 2.0 ** -33
+    ref = math.sqrt(2.0) * special.erfcinv(2 * p) * np.where(neg, -1.0, 1.0)
+    core = np.abs(ref) < 5.0
+    assert np.max(np.abs(got - ref)[core]) < 5e-6          # single-precision polynomial
+    assert np.max(np.abs(got / ref - 1)[~core]) < 1e-3      # extreme tails (p < 3e-7)
+    assert abs(got.mean()) < 0.03 and abs(got[:20000].std() - 1) < 0.03
+
+
+def test_root6(oracle):
+    for x in (1e-6, 0.3, 1.0, 3.0, 1e6):
+        assert abs(oracle.lib.pda_oracle_root6f(x) - x ** (1 / 6)) <= 2e-7 * x ** (1 / 6)
+    assert oracle.lib.pda_oracle_root6f(0.0) == 0.0 and oracle.lib.pda_oracle_root6f(-1.0) == 0.0
+
+
+def test_hist_is_boost_regular_axis(oracle):
+    # values probed against boost::histogram in the survey: 0.0049f -> 0, 0.5 -> 100,
+    # 0.99999 -> 199, 1.0 / NaN -> overflow, < 0 -> underflow (SURVEY.md §8c probe 2)
+    x = np.array([0.0049, 0.5, 0.99999, 1.0, np.nan, -0.1, 0.0, 5.0, -0.0], np.float32)
+    h = oracle.hist(x, 200)
+    assert h[0] == 3 and h[100] == 1 and h[199] == 1 and h[200] == 3 and h[201] == 1
+    assert h.sum() == x.size
+
+
+def test_chi2_hand_computed(oracle):
+    nb, R, lp, n = 6, 2, 1, 2
+    O = np.array([9, 5, 4, 0, 7, 3], np.float32)
+    M = np.array([100, 8, 0, 6, 10, 0, 55, 66], np.uint64)  # + overflow, underflow entries
+    eff, s = nb - lp, np.float32(0)
+    for i in range(lp, nb):
+        if M[i] > 0:
+            m = np.float32(M[i]) / np.float32(R)
+            d = np.float32(O[i] - m)
+            s = np.float32(np.float64(s) + np.float64(d) * np.float64(d) / np.float64(m))
+        else:
+            eff -= 1
+    want = np.float32(s / np.float32(eff - n * (n + 1)))
+    got = np.float32(oracle.chi2(O, M, nb, R, lp, n))
+    assert got == want or (np.isnan(got) and np.isnan(want)) or np.isinf(got) == np.isinf(want)
+
+
+def test_params_reject_bad_counts(oracle):
+    assert oracle.params(2, [0.3, 0.7, 1, 2, 1]) is None          # n*n+n = 6 expected
+    assert oracle.params(1, [0.3, 1.0]) is None                   # genMatK: empty rate list
+    assert oracle.params(3, np.ones(12, np.float32)) is not None
+
+
+def test_binomial_edge_cases(oracle):
+    import ctypes as C
+    st = (C.c_uint32 * 4)()
+    oracle.lib.pda_oracle_rk_seed(12345, st)
+    assert oracle.lib.pda_oracle_binomial(st, 0, 0.3) == 0
+    assert oracle.lib.pda_oracle_binomial(st, 0, 0.9) == 0
+    assert oracle.lib.pda_oracle_binomial(st, -2, 0.3) == 0
+    assert oracle.lib.pda_oracle_binomial(st, -2, 0.9) == -2   # n - inversion(n, q): the reference's result
+    for n, p in ((5, 0.2), (5, 0.8), (200, 0.4), (200, 0.7), (1000, 0.5)):
+        xs = [oracle.lib.pda_oracle_binomial(st, n, p) for _ in range(400)]
+        assert all(0 <= v <= n for v in xs)
+        assert abs(np.mean(xs) - n * p) < 5 * math.sqrt(n * p * (1 - p) / 400) + 1e-9
