@@ -59,7 +59,15 @@ class ClockSampler:
     def __init__(self, gpu_index: int):
         self.idx = gpu_index
         self.proc = None
-        self.lines = []
+        self.lines = []   # (arrival time, csv line)
+        self.t_begin = None
+        self.t_end = None
+
+    def mark_begin(self):
+        self.t_begin = time.perf_counter()
+
+    def mark_end(self):
+        self.t_end = time.perf_counter()
 
     def start(self):
         try:
@@ -73,7 +81,7 @@ class ClockSampler:
 
     def _pump(self):
         for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
+            self.lines.append((time.perf_counter(), ln.strip()))
 
     def stop(self):
         if self.proc is None:
@@ -86,7 +94,13 @@ class ClockSampler:
             self.proc.kill()
         sm, smax, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        inside = [ln for (t, ln) in self.lines
+                  if self.t_begin is not None and self.t_begin - 0.05 <= t <= (self.t_end or t) + 0.15]
+        window = "timed regions"
+        if len(inside) < 3:   # a very short run: fall back to everything since the warm-up
+            inside = [ln for (_, ln) in self.lines]
+            window = "warm-up + timed regions (timed regions shorter than 3 samples)"
+        for ln in inside:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
                 continue
@@ -99,7 +113,7 @@ class ClockSampler:
                     reasons.add(nm)
         return {"sm_mhz": float(np.median(sm)) if sm else None,
                 "sm_max_mhz": float(max(smax)) if smax else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "window": window, "reasons": sorted(reasons)}
 
 
 def cpu_leg(w, sample_bursts, R, seconds_hint=12.0):
@@ -174,8 +188,8 @@ def run_reference(args, w, rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cfg", type=int, default=2)
     ap.add_argument("--bursts", type=int, default=None, help="override bursts per GPU")
@@ -250,22 +264,22 @@ def main():
     # resident parameters for the device-timed leg
     chi2_first, hist_first = mc.evaluate(n, arg0, sid=0)
     assert int(hist_first.sum()) == samples_job, (int(hist_first.sum()), samples_job)
-    for _ in range(args.warmup):
+    clocks = ClockSampler(local_rank)
+    clocks.start()              # nvidia-smi needs ~0.5 s to come up: start it before the warm-up
+    for _ in range(max(args.warmup, 3)):
         step_resident()
     l0 = mc.launch_count()
-    clocks = ClockSampler(local_rank)
     barrier()
-    clocks.start()
+    clocks.mark_begin()
     t_wall0 = time.perf_counter()
     ms = [step_resident() for _ in range(args.steps)]
     barrier()
     t_wall = time.perf_counter() - t_wall0
-    clk = clocks.stop()
     launches = mc.launch_count() - l0
     dev_ms = float(sum(ms))
 
     # end to end through the public API, host buffers in and out
-    for _ in range(args.warmup):
+    for _ in range(max(args.warmup, 3)):
         step_e2e()
     barrier()
     t0 = time.perf_counter()
@@ -273,6 +287,8 @@ def main():
         chi2_last, hist_last = step_e2e()
     barrier()
     e2e_s = time.perf_counter() - t0
+    clocks.mark_end()
+    clk = clocks.stop()
     assert int(hist_last.sum()) == samples_job
 
     if world > 1:

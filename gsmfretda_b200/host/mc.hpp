@@ -1,0 +1,186 @@
+// mc.hpp — the reference's `class mc` (/root/reference/src/mc.hpp:78-179) re-created on top of
+// the C ABI of include/gsmfret_c.h.  Same public members, argument meaning and error
+// behaviour, so that code written against the reference — gpuWorker::run
+// (/root/reference/src/gpuWorker.cpp:38-87), the result-reading part of streamWorker::run
+// (/root/reference/src/streamWorker.cpp:186-206), main (/root/reference/src/main.cpp:129-160)
+// — compiles against it unchanged.  Header-only; link with libgsmfret.so.
+//
+// Differences, all additive:
+//   * hHist(sid) / hChi2(sid): the histogram and reduced chi-square the fused kernel already
+//     produced, so a caller no longer needs hmcE and the host histogram loop;
+//   * mc::Options chooses whether hmcE is kept (default: yes, for drop-in compatibility);
+//   * set_reSampleTimes keeps the reference's rounding down to a power of two; use
+//     set_reSampleTimes_exact for any R (the new kernel has no such restriction).
+#pragma once
+#include <atomic>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cmath>
+#include <vector>
+
+#include "../../include/gsmfret_c.h"
+
+#ifndef __DRIVER_TYPES_H__
+typedef struct CUstream_st* cudaStream_t;
+#endif
+
+typedef float retype;  // /root/reference/src/loadHdf5.hpp:8
+
+// The reference's convention (/root/reference/src/cuda_tools.hpp:20-28): print
+// "<stmt> returned <msg> at file:line" and leave the process.
+#define GSM_CHECK_RETURN(stmt)                                                              \
+    do {                                                                                    \
+        int gsm_rc_ = (stmt);                                                               \
+        if (gsm_rc_ < 0) {                                                                  \
+            std::fprintf(stderr, "%s returned %s(%d) at %s:%d\n", #stmt, gsm_last_error(), \
+                         gsm_rc_, __FILE__, __LINE__);                                      \
+            std::exit(EXIT_FAILURE);                                                        \
+        }                                                                                   \
+    } while (0)
+
+class mc {
+  public:
+    struct Options {
+        bool keep_mce = true;      // fill hmcE[sid] like the reference (costs an N*R-float copy per run)
+        bool force_raw64 = false;  // keep the reference's 16 B/photon layout
+        uint32_t seed = 0x9E3779B9u;
+        int fret_hist_num = 200;   // cmdline.ggo:14
+        int left_pad = 2;          // main.cpp:155
+    };
+
+    int devid;
+    char gpuuuid[33];
+    std::atomic_int workerNum;
+    retype** hmcE;
+    int* s_n;
+    int sz_burst;
+    int reSampleTimes;
+
+    mc(int id, int _streamNum = 16, unsigned char debug = 0, std::uintmax_t hdf5size = 0,
+       bool profiler = false)
+        : mc(id, _streamNum, debug, hdf5size, profiler, Options()) {}
+
+    mc(int id, int _streamNum, unsigned char /*debug*/, std::uintmax_t /*hdf5size*/, bool /*profiler*/,
+       const Options& opt)
+        : devid(id), hmcE(nullptr), s_n(nullptr), sz_burst(0), reSampleTimes(4), ctx(nullptr),
+          streamNum(0), streams(nullptr)
+    {
+        gpuuuid[0] = 0;
+        unsigned flags = (opt.keep_mce ? GSM_KEEP_MCE : 0u) | (opt.force_raw64 ? GSM_FORCE_RAW64 : 0u);
+        int rc = gsm_create(id, _streamNum, flags, &ctx);
+        if (rc == GSM_EINVAL) {  // "gpu id set error!" (mc.cu:228-231): the reference returns quietly
+            std::printf("gpu id set error!\n");
+            workerNum.store(_streamNum);
+            return;
+        }
+        GSM_CHECK_RETURN(rc);
+        streamNum = gsm_stream_count(ctx);
+        workerNum.store(streamNum);
+        gsm_device_uuid(ctx, gpuuuid);
+        GSM_CHECK_RETURN(gsm_set_seed(ctx, opt.seed));
+        GSM_CHECK_RETURN(gsm_set_hist(ctx, opt.fret_hist_num, opt.left_pad));
+        GSM_CHECK_RETURN(gsm_set_resample_times(ctx, reSampleTimes));
+        streams = new cudaStream_t[streamNum];
+        hmcE = new retype*[streamNum]();
+        s_n = new int[streamNum]();
+        for (int i = 0; i < streamNum; ++i) streams[i] = (cudaStream_t)gsm_stream(ctx, i);
+    }
+
+    ~mc()
+    {
+        gsm_destroy(ctx);
+        delete[] streams;
+        delete[] hmcE;
+        delete[] s_n;
+    }
+    mc(const mc&) = delete;
+    mc& operator=(const mc&) = delete;
+
+    void set_gpuid() { GSM_CHECK_RETURN(gsm_set_device(ctx)); }
+
+    cudaStream_t* getStreams(int* numStream = nullptr)
+    {
+        if (numStream) *numStream = streamNum;
+        return streams;
+    }
+
+    bool streamQuery(int sid)
+    {
+        if (sid < 0 || sid >= streamNum) return false;
+        int r = gsm_query(ctx, sid);
+        GSM_CHECK_RETURN(r);
+        return r == 1;
+    }
+
+    int set_nstates(int n, int sid)
+    {
+        int r = gsm_set_nstates(ctx, n, sid);
+        GSM_CHECK_RETURN(r);
+        s_n[sid] = n;
+        return r;  // the previous n (== n when unchanged), as mc::set_nstates
+    }
+
+    bool set_params(int n, int sid, std::vector<float>& args)
+    {
+        int r = gsm_set_params(ctx, n, sid, args.data(), (int)args.size());
+        GSM_CHECK_RETURN(r);
+        return r == 1;
+    }
+
+    int setBurstBd(int cstart, int cstop, int sid)
+    {
+        int r = gsm_set_burst_bd(ctx, cstart, cstop, sid);
+        if (r < -1) GSM_CHECK_RETURN(r);
+        return r;
+    }
+
+    // reSampleTimes = 2^floor(log2 t), /root/reference/src/mc.cu:316
+    void set_reSampleTimes(int t)
+    {
+        int r = 1;
+        while (r * 2 <= t) r *= 2;
+        set_reSampleTimes_exact(r);
+    }
+    void set_reSampleTimes_exact(int t)
+    {
+        GSM_CHECK_RETURN(gsm_set_resample_times(ctx, t));
+        reSampleTimes = t;
+    }
+
+    void init_randstate(int N, int sid) { GSM_CHECK_RETURN(gsm_init_randstate(ctx, N, sid)); }
+    void set_params_buff(int oldS_n, int N_sid, int sid) { GSM_CHECK_RETURN(gsm_set_params_buff(ctx, oldS_n, N_sid, sid)); }
+
+    void run_kernel(int N, int sid)
+    {
+        GSM_CHECK_RETURN(gsm_run(ctx, N, sid));
+        hmcE[sid] = const_cast<retype*>(gsm_result_mcE(ctx, sid));  // pinned; valid once streamQuery(sid)
+    }
+
+    void get_res(int /*sid*/, int /*N*/) {}  // debug print in the reference (mc.cu:602-617)
+    void free_data_gpu() {}                  // all device memory is released by ~mc
+
+    void init_data_gpu(std::vector<int64_t>& istart, std::vector<int64_t>& start, std::vector<int64_t>& stop,
+                       std::vector<int>& phCount, long _sz_tag, int64_t* burst_ad, int64_t* burst_dd,
+                       std::vector<float>& T_burst_duration, std::vector<float>& SgDivSr, float& iclk_p,
+                       float& ibg_ad_rate, float& ibg_dd_rate)
+    {
+        GSM_CHECK_RETURN(gsm_init_data(ctx, (int64_t)start.size(), istart.data(), start.data(), stop.data(),
+                                       phCount.data(), (int64_t)_sz_tag, burst_ad, burst_dd,
+                                       T_burst_duration.data(), SgDivSr.data(), iclk_p, ibg_ad_rate,
+                                       ibg_dd_rate, 0));
+        sz_burst = (int)start.size();
+    }
+
+    bool get_max_conversion_capacity(int max_stateNum = 8) { return gsm_get_max_conversion_capacity(ctx, max_stateNum) == 1; }
+
+    // ---- additions -------------------------------------------------------------------
+    const uint64_t* hHist(int sid, int p = 0) const { return gsm_result_hist(ctx, sid, p); }
+    float hChi2(int sid) const { return gsm_result_chi2(ctx, sid); }
+    gsm_ctx* handle() { return ctx; }
+
+  protected:
+    gsm_ctx* ctx;
+    int streamNum;
+    cudaStream_t* streams;
+};

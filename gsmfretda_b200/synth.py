@@ -181,3 +181,15 @@ def workload(cfg: int, n_bursts: int | None = None, R: int | None = None,
     if P is not None and cfg != 4:
         w.args = np.repeat(w.args, P, axis=0)
     return w
+
+
+def save_bin(b: Bursts, path: str) -> None:
+    """Flat binary dump read by gsmfretda_b200/host/local_node.cpp (format in its header)."""
+    import struct
+    with open(path, "wb") as f:
+        f.write(b"GSMB")
+        f.write(struct.pack("<Iqq4f", 1, b.n_bursts, b.n_photons, float(b.clk_p), float(b.bg_ad_rate),
+                            float(b.bg_dd_rate), 0.0))
+        for a, dt in ((b.start, np.int64), (b.stop, np.int64), (b.istart, np.int64), (b.ph_count, np.int32),
+                      (b.T, np.float32), (b.SgDivSr, np.float32), (b.burst_ad, np.int64), (b.burst_dd, np.int64)):
+            np.ascontiguousarray(a, dtype=dt).tofile(f)

@@ -1,0 +1,65 @@
+"""The C++ host side (gsmfretda_b200/host): `class mc` with the reference's signatures over the
+C ABI, the gpuWorker state machine, and local_node (parameter threads + gpuWorker thread)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from gsmfretda_b200 import synth
+from helpers import NB, LEFT_PAD
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HOST = os.path.join(ROOT, "gsmfretda_b200", "host")
+
+
+def build():
+    subprocess.run(["make", "-s", "-C", HOST], check=True)
+    return os.path.join(HOST, "local_node")
+
+
+def test_shim_compiles_and_links():
+    exe = build()
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 2 and "usage" in r.stderr
+
+
+def test_shim_declares_the_reference_members():
+    src = open(os.path.join(HOST, "mc.hpp")).read()
+    for member in ("void set_gpuid()", "cudaStream_t* getStreams(int* numStream", "bool streamQuery(int sid)",
+                   "int set_nstates(int n, int sid)", "bool set_params(int n, int sid, std::vector<float>& args)",
+                   "int setBurstBd(int cstart, int cstop, int sid)", "void set_reSampleTimes(int t)",
+                   "void init_randstate(int N, int sid)", "void run_kernel(int N, int sid)",
+                   "void set_params_buff(int oldS_n, int N_sid, int sid)", "void init_data_gpu(",
+                   "bool get_max_conversion_capacity(int max_stateNum = 8)", "std::atomic_int workerNum",
+                   "retype** hmcE", "int* s_n", "int sz_burst", "int reSampleTimes", "char gpuuuid[33]"):
+        assert member in src, member
+
+
+@pytest.mark.gpu
+def test_local_node_matches_oracle(oracle, tmp_path):
+    exe = build()
+    w = synth.workload(4, n_bursts=1200, R=8, P=10)
+    b = w.bursts()
+    synth.save_bin(b, str(tmp_path / "b.bin"))
+    with open(tmp_path / "p.txt", "w") as f:
+        for a in w.args:
+            f.write("2 " + " ".join(repr(float(x)) for x in a) + "\n")
+        f.write("3 " + " ".join(repr(float(x)) for x in synth.workload(3).args[0]) + "\n")   # n changes mid-run
+    r = subprocess.run([exe, str(tmp_path / "b.bin"), str(tmp_path / "p.txt"), str(tmp_path / "o.txt"), "3", "8", "42"],
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    assert "param-evals/s" in r.stdout
+    rows = [l.split() for l in open(tmp_path / "o.txt") if l.strip()]
+    assert len(rows) == 11
+    ohist = oracle.observed_hist(b, NB)
+    allargs = [(2, a) for a in w.args] + [(3, synth.workload(3).args[0])]
+    for row in rows:
+        ji, epoch, chi2 = int(row[0]), int(row[2]), float(row[3])
+        hist = np.array([int(x) for x in row[4:]], np.uint64)
+        n, a = allargs[ji]
+        o = oracle.eval(b, n, a, 8, 42, epoch)
+        oh = oracle.hist(o["mcE"], NB)
+        assert np.array_equal(hist, oh)
+        c = oracle.chi2(ohist, oh, NB, 8, LEFT_PAD, n)
+        assert abs(chi2 - c) <= 2e-6 * abs(c)
