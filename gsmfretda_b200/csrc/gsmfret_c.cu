@@ -600,8 +600,7 @@ int gsm_init_randstate(gsm_ctx* c, int, int sid)
 {
     int r = check_sid(c, sid);
     if (r) return r;
-    c->slots[sid].epoch += 1u << 16;  // a fresh block of draw epochs, as a re-seed would give
-    return GSM_OK;
+    return GSM_OK;  // nothing to build: the draw epoch already advances with every run
 }
 
 int gsm_set_params_buff(gsm_ctx* c, int, int, int sid) { return check_sid(c, sid); }

@@ -106,8 +106,8 @@ int gsm_set_params(gsm_ctx* ctx, int n, int sid, const float* args, int n_args);
 /* mc::setBurstBd(cstart, cstop, sid) -> N (-1 if cstart == -1)   mc.cu:523-566
  * As in the reference the evaluated bursts are [0, N): the range start is not applied (quirk Q7). */
 int gsm_set_burst_bd(gsm_ctx* ctx, int cstart, int cstop, int sid);
-/* mc::init_randstate(N, sid)   mc.cu:366-455 : nothing to allocate with a counter-based
- * generator; starts a new draw epoch for the slot. */
+/* mc::init_randstate(N, sid)   mc.cu:366-455 : nothing to allocate or seed with a
+ * counter-based generator (the draw epoch advances with every run); no-op */
 int gsm_init_randstate(gsm_ctx* ctx, int N, int sid);
 /* mc::set_params_buff(oldS_n, N_sid, sid)   mc.cu:783-789 : no scratch needed; no-op */
 int gsm_set_params_buff(gsm_ctx* ctx, int old_n, int N_sid, int sid);

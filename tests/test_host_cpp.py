@@ -60,6 +60,6 @@ def test_local_node_matches_oracle(oracle, tmp_path):
         n, a = allargs[ji]
         o = oracle.eval(b, n, a, 8, 42, epoch)
         oh = oracle.hist(o["mcE"], NB)
-        assert np.array_equal(hist, oh)
+        assert np.array_equal(hist, oh), (ji, epoch, int(hist.sum()), int(oh.sum()))
         c = oracle.chi2(ohist, oh, NB, 8, LEFT_PAD, n)
         assert abs(chi2 - c) <= 2e-6 * abs(c)
