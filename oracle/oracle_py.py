@@ -2,6 +2,7 @@
 
     libpda_oracle.so      the C restatement (oracle/pda_oracle.c)
     _ref/libref_cpu.so    the reference's own sources compiled for the host (oracle/ref_shim.cpp)
+    _ref/libref_gpu.so    the reference's `class mc` unmodified for sm_100a (oracle/ref_gpu_shim.cpp)
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
 import this module.  Nothing under gsmfretda_b200/ does.
@@ -45,6 +46,7 @@ def build(ref: bool = True) -> None:
     subprocess.run(["make", "-s", "-C", HERE, "all"], check=True)
     if ref and os.path.isdir("/root/reference/src"):
         subprocess.run(["make", "-s", "-C", HERE, "ref"], check=True)
+        subprocess.run(["make", "-s", "-C", HERE, "refgpu"], check=True)
 
 
 def _ptr(a, t):
@@ -215,3 +217,55 @@ class Ref:
 
 def have_ref() -> bool:
     return os.path.exists(os.path.join(HERE, "_ref", "libref_cpu.so"))
+
+
+def have_refgpu() -> bool:
+    return os.path.exists(os.path.join(HERE, "_ref", "libref_gpu.so"))
+
+
+class RefGpu:
+    """The reference's own `class mc` on the GPU (cuRAND Sobol64 + libdevice).  Its destructor
+    calls cudaDeviceReset(): use it from a process of its own (oracle/refgpu_run.py) and never
+    next to another CUDA user."""
+
+    def __init__(self, devid=0, streams=1):
+        path = os.path.join(HERE, "_ref", "libref_gpu.so")
+        if not os.path.exists(path):
+            raise FileNotFoundError(path)
+        L = self.lib = C.CDLL(path)
+        L.refgpu_create.argtypes = [C.c_int, C.c_int]; L.refgpu_create.restype = C.c_void_p
+        L.refgpu_destroy.argtypes = [C.c_void_p]
+        L.refgpu_set_resample.argtypes = [C.c_void_p, C.c_int]
+        L.refgpu_resample.argtypes = [C.c_void_p]; L.refgpu_resample.restype = C.c_int
+        L.refgpu_init_data.argtypes = [C.c_void_p, C.c_int64, _i64p, _i64p, _i64p, _i32p, C.c_int64,
+                                       _i64p, _i64p, _f32p, _f32p, C.c_float, C.c_float, C.c_float]
+        L.refgpu_launch.argtypes = [C.c_void_p, C.c_int, _f32p, C.c_int]; L.refgpu_launch.restype = C.c_int
+        L.refgpu_query.argtypes = [C.c_void_p, C.c_int]; L.refgpu_query.restype = C.c_int
+        L.refgpu_hmcE.argtypes = [C.c_void_p, C.c_int]; L.refgpu_hmcE.restype = _f32p
+        L.refgpu_time.argtypes = [C.c_void_p, C.c_int, _f32p, C.c_int, C.c_int]; L.refgpu_time.restype = C.c_double
+        self.h = L.refgpu_create(devid, streams)
+        self._keep = None
+
+    def set_reSampleTimes(self, R):
+        self.lib.refgpu_set_resample(self.h, R)
+        return int(self.lib.refgpu_resample(self.h))
+
+    def init_bursts(self, b):
+        self._keep = b
+        self.lib.refgpu_init_data(self.h, b.n_bursts, _ptr(b.istart, _i64p), _ptr(b.start, _i64p),
+                                  _ptr(b.stop, _i64p), _ptr(b.ph_count, _i32p), b.burst_ad.shape[0],
+                                  _ptr(b.burst_ad, _i64p), _ptr(b.burst_dd, _i64p), _ptr(b.T, _f32p),
+                                  _ptr(b.SgDivSr, _f32p), float(b.clk_p), float(b.bg_ad_rate),
+                                  float(b.bg_dd_rate))
+
+    def evaluate(self, n, args, sid=0) -> np.ndarray:
+        a = np.ascontiguousarray(args, np.float32)
+        N = self.lib.refgpu_launch(self.h, n, _ptr(a, _f32p), sid)
+        while not self.lib.refgpu_query(self.h, sid):
+            pass
+        R = int(self.lib.refgpu_resample(self.h))
+        return np.ctypeslib.as_array(self.lib.refgpu_hmcE(self.h, sid), shape=(N * R,)).copy()
+
+    def time(self, n, args, K, sid=0) -> float:
+        a = np.ascontiguousarray(args, np.float32)
+        return float(self.lib.refgpu_time(self.h, n, _ptr(a, _f32p), sid, K))
