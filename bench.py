@@ -195,6 +195,8 @@ def main():
     ap.add_argument("--bursts", type=int, default=None, help="override bursts per GPU")
     ap.add_argument("--repeats", type=int, default=None)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--mode", default="replay", choices=["replay", "normal"],
+                    help="replay: bit-exact draw contract (FP64 binomial); normal: FP32 fast arithmetic")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -230,6 +232,7 @@ def main():
     mc.set_reSampleTimes(R)
     mc.set_seed(SEED)
     mc.set_hist(NB, LEFT_PAD)
+    mc.set_mode(capi.GSM_MODE_NORMAL if args.mode == "normal" else capi.GSM_MODE_REPLAY)
     mc.init_bursts(b, g_offset=rank * B)
     if world > 1:
         idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
@@ -309,7 +312,9 @@ def main():
             "metric": "burst-samples/s", "value": value, "unit": "burst-samples/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32 walk + f64 binomial (replay arithmetic), u32/u64 histogram",
+            "dtype": ("f32 walk + f64 binomial (replay arithmetic), u32/u64 histogram" if args.mode == "replay"
+                      else "f32 (normal mode: hardware lg2/ex2/rcp, f32 binomial inversion), u32/u64 histogram"),
+            "mode": args.mode,
             "data": "synthetic",
             "config": {"workload": w.name, "bursts_per_gpu": B, "photons_per_gpu": b.n_photons,
                        "repeats": R, "states": n, "param_vectors": 1, "hist_bins": NB,

@@ -18,6 +18,8 @@ GSM_KEEP_MCE = 1
 GSM_KEEP_COUNTS = 2
 GSM_FORCE_RAW64 = 4
 GSM_NO_INDEX = 8
+GSM_MODE_REPLAY = 0
+GSM_MODE_NORMAL = 1
 
 _f32p = C.POINTER(C.c_float)
 _f64p = C.POINTER(C.c_double)
@@ -42,6 +44,8 @@ SIGNATURES = {
     "gsm_set_resample_times": (C.c_int, [_ctx, C.c_int]),
     "gsm_resample_times": (C.c_int, [_ctx]),
     "gsm_set_seed": (C.c_int, [_ctx, C.c_uint32]),
+    "gsm_set_mode": (C.c_int, [_ctx, C.c_int]),
+    "gsm_mode": (C.c_int, [_ctx]),
     "gsm_set_hist": (C.c_int, [_ctx, C.c_int, C.c_int]),
     "gsm_init_data": (C.c_int, [_ctx, C.c_int64, _i64p, _i64p, _i64p, _i32p, C.c_int64, _i64p, _i64p,
                                 _f32p, _f32p, C.c_float, C.c_float, C.c_float, C.c_int64]),
@@ -174,6 +178,13 @@ class Mc:
 
     def set_seed(self, seed: int):
         self._ck(self.lib.gsm_set_seed(self._h, seed & 0xFFFFFFFF))
+
+    def set_mode(self, mode: int):
+        """GSM_MODE_REPLAY (bit-exact draw contract) or GSM_MODE_NORMAL (FP32 fast arithmetic)."""
+        self._ck(self.lib.gsm_set_mode(self._h, int(mode)))
+
+    def mode(self) -> int:
+        return int(self.lib.gsm_mode(self._h))
 
     def set_hist(self, n_bins: int = 200, left_pad: int = 2):
         self._ck(self.lib.gsm_set_hist(self._h, n_bins, left_pad))

@@ -118,6 +118,7 @@ struct gsm_ctx {
     int64_t B = 0, n_photons = 0, g_offset = 0;
     bool packed = false, with_bg = false;
     int layout = 0;  // 0 raw int64 ticks, 1 packed words, 2 packed words + index
+    int mode = 0;    // GSM_MODE_REPLAY / GSM_MODE_NORMAL
     float clk_p = 0, bg_ad = 0, bg_dd = 0;
     BurstRec* d_bursts = nullptr;
     int32_t* d_pk = nullptr;
@@ -384,6 +385,19 @@ int gsm_set_seed(gsm_ctx* c, uint32_t seed)
     return GSM_OK;
 }
 
+int gsm_set_mode(gsm_ctx* c, int mode)
+{
+    if (!c) return fail(GSM_EINVAL, "null context");
+    if (mode != GSM_MODE_REPLAY && mode != GSM_MODE_NORMAL) return fail(GSM_EINVAL, "unknown mode %d", mode);
+    if (mode != c->mode) {
+        for (Slot& s : c->slots) CK(cudaStreamSynchronize(s.stream));
+        c->mode = mode;
+        if (c->inited) c->cfg = eval_launch_cfg(c->devid, c->layout, c->with_bg, c->nb, c->mode);
+    }
+    return GSM_OK;
+}
+int gsm_mode(const gsm_ctx* c) { return c ? c->mode : -1; }
+
 int gsm_set_hist(gsm_ctx* c, int n_bins, int left_pad)
 {
     if (!c || n_bins < 1 || n_bins + 2 > 1024 || left_pad < 0 || left_pad > n_bins)
@@ -399,7 +413,7 @@ int gsm_set_hist(gsm_ctx* c, int n_bins, int left_pad)
             s.ran = false;
         }
         if (c->inited) {
-            c->cfg = eval_launch_cfg(c->devid, c->layout, c->with_bg, c->nb);
+            c->cfg = eval_launch_cfg(c->devid, c->layout, c->with_bg, c->nb, c->mode);
             return build_observed(c);
         }
     }
@@ -517,7 +531,7 @@ int gsm_init_data(gsm_ctx* c, int64_t B, const int64_t* istart, const int64_t* s
     c->packed = packed; c->with_bg = with_bg;
     c->layout = packed ? (indexed ? 2 : 1) : 0;
     c->clk_p = clk_p; c->bg_ad = bg_ad_rate; c->bg_dd = bg_dd_rate;
-    c->cfg = eval_launch_cfg(c->devid, c->layout, with_bg, c->nb);
+    c->cfg = eval_launch_cfg(c->devid, c->layout, with_bg, c->nb, c->mode);
     c->inited = true;
     for (Slot& s : c->slots) { s.N = -1; s.ran = false; }
     return build_observed(c);
@@ -645,7 +659,7 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
         CK(cudaMemcpyAsync(s.d_params, s.h_params, (size_t)s.P * sizeof(ParamRaw), cudaMemcpyHostToDevice, s.stream));
         s.params_resident = true;
     }
-    CK(launch_eval(a, c->layout, c->with_bg, c->cfg, s.stream));
+    CK(launch_eval(a, c->layout, c->with_bg, c->cfg, s.stream, c->mode));
     c->launches += 1;
     if (c->comm) {
         int e = g_nccl.AllReduce(s.d_whist, s.d_whist, (size_t)s.P * nbp, kNcclUint64, kNcclSum, c->comm, s.stream);

@@ -67,8 +67,12 @@ struct LaunchCfg {
 
 // how many blocks to launch (persistent grid: SMs x resident blocks)
 // layout: 0 raw int64 ticks, 1 packed words scanned linearly, 2 packed words + index
-LaunchCfg eval_launch_cfg(int device, int layout, bool with_bg, int nb);
-cudaError_t launch_eval(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s);
+// mode: 0 replay (bit-exact draw contract), 1 normal (FP32 fast arithmetic)
+LaunchCfg eval_launch_cfg(int device, int layout, bool with_bg, int nb, int mode);
+cudaError_t launch_eval(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s, int mode);
+// the normal-mode instantiation lives in its own translation unit (pda_kernels_fast.cu, fmad on)
+LaunchCfg eval_launch_cfg_fast(int device, int layout, bool with_bg, int nb);
+cudaError_t launch_eval_fast(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s);
 // chi2 + copy-out + reset of the working histogram (used after a cross-GPU reduction)
 cudaError_t launch_finalize(const EvalArgs& a, cudaStream_t s);
 

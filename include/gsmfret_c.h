@@ -73,6 +73,17 @@ int gsm_set_resample_times(gsm_ctx* ctx, int R);
 int gsm_resample_times(const gsm_ctx* ctx);
 /* key of the counter-based generator; the reference seeds from cuRAND tables (mc.cu:366-455) */
 int gsm_set_seed(gsm_ctx* ctx, uint32_t seed);
+/* Arithmetic mode of the evaluation (no counterpart in the reference, whose only mode is
+ * libdevice logf/powf + FP64 rk_binomial on cuRAND Sobol draws, mc.cu:83-197):
+ *   GSM_MODE_REPLAY  deterministic replay: explicit-rounding arithmetic, FP64 binomial on the
+ *                    xor128 stream; integer counts, bins and chi-square bits equal the oracle's
+ *   GSM_MODE_NORMAL  FP32 arithmetic on the hardware lg2/ex2/rcp units, FP32 binomial inversion;
+ *                    same distributions (KS p > 0.01, chi-square within 1 %), about 2-3x faster
+ * Results of either mode are a pure function of (data, parameters, seed, epoch). */
+#define GSM_MODE_REPLAY 0
+#define GSM_MODE_NORMAL 1
+int gsm_set_mode(gsm_ctx* ctx, int mode);
+int gsm_mode(const gsm_ctx* ctx);
 /* fretHistNum / leftPad of streamWorker (streamWorker.cpp:41,62-70; main.cpp:155); defaults 200, 2 */
 int gsm_set_hist(gsm_ctx* ctx, int n_bins, int left_pad);
 

@@ -1,0 +1,166 @@
+"""Normal mode (GSM_MODE_NORMAL: FP32 arithmetic on the hardware lg2/ex2/rcp units, FP32
+binomial inversion) against the oracle's replay arithmetic.  North-star bar for this mode:
+E histograms agree within Monte-Carlo standard error — two-sample KS p > 0.01 and reduced
+chi-square within 1 % — with INDEPENDENT draws on the two sides (different seeds; sharing the
+seed would correlate the walks and make the test pass trivially)."""
+import numpy as np
+import pytest
+
+from gsmfretda_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+NB, LEFT_PAD = 200, 2
+
+
+def run(gsm, b, n, args, R, seed, epoch, mode, keep=True, **kw):
+    with gsm.Mc(0, 2, keep_mce=keep, keep_counts=keep, **kw) as mc:
+        mc.set_reSampleTimes(R)
+        mc.set_seed(seed)
+        mc.set_hist(NB, LEFT_PAD)
+        mc.set_mode(mode)
+        assert mc.mode() == mode
+        mc.init_bursts(b)
+        chi2, hist = mc.evaluate(n, args, sid=0, epoch=epoch)
+        tot = b.n_bursts * R
+        out = dict(chi2=chi2, hist=hist.copy(), flags=mc.flags(0))
+        if keep:
+            out.update(mcE=mc.hmcE(0, tot).copy(), sum_ai=mc.counts(0, tot).copy(), n_steps=mc.steps(0, tot).copy())
+        return out
+
+
+def ks(a, b):
+    from scipy import stats
+    r = stats.ks_2samp(a, b, method="asymp")
+    return float(r.statistic), float(r.pvalue)
+
+
+# (cfg, bursts, R): about 1e6 samples per side
+CASES = [(1, 16000, 64), (2, 10000, 100), (3, 60000, 16), (5, 120000, 8)]
+
+
+@pytest.mark.parametrize("cfg,nb,R", CASES)
+def test_normal_vs_oracle_replay_statistics(gsm, oracle, cfg, nb, R):
+    w = synth.workload(cfg, n_bursts=nb, R=R)
+    b = w.bursts()
+    g = run(gsm, b, w.n_states, w.args[0], R, seed=101, epoch=1, mode=gsm.GSM_MODE_NORMAL)
+    o = oracle.eval(b, w.n_states, w.args[0], R, 202, 1)            # independent draws
+    assert g["flags"] == 0
+    assert int(g["hist"].sum()) == nb * R
+    assert np.all(np.isfinite(g["mcE"]))
+    D, p = ks(g["mcE"], o["mcE"])
+    assert p > 0.01, (D, p)
+    oh = oracle.hist(o["mcE"], NB)
+    ohist = oracle.observed_hist(b, NB)
+    c_o = oracle.chi2(ohist, oh, NB, R, LEFT_PAD, w.n_states)
+    assert abs(g["chi2"] - c_o) / c_o < 0.01, (g["chi2"], c_o)
+    # the fused histogram is the histogram of the per-sample values it returns
+    assert np.array_equal(g["hist"], oracle.hist(g["mcE"], NB))
+    # integer bookkeeping: mean acceptor counts and dwell steps agree to MC error
+    se = o["sum_ai"].std() / np.sqrt(o["sum_ai"].size)
+    assert abs(g["sum_ai"].mean() - o["sum_ai"].mean()) < 6 * se + 1e-9
+    se = o["n_steps"].std() / np.sqrt(o["n_steps"].size)
+    assert abs(g["n_steps"].mean() - o["n_steps"].mean()) < 6 * se + 1e-9
+
+
+@pytest.mark.parametrize("cfg,nb,R", [(2, 4000, 16), (5, 4000, 4)])
+def test_normal_same_walk_as_replay(gsm, cfg, nb, R):
+    """Both modes key Philox the same way, so with the same seed the Markov walk (state picks,
+    window edges) is the same up to float rounding of the dwell times: step counts agree on
+    almost every sample, and E is strongly correlated."""
+    w = synth.workload(cfg, n_bursts=nb, R=R)
+    b = w.bursts()
+    a = run(gsm, b, w.n_states, w.args[0], R, 7, 5, gsm.GSM_MODE_NORMAL)
+    r = run(gsm, b, w.n_states, w.args[0], R, 7, 5, gsm.GSM_MODE_REPLAY)
+    assert (a["n_steps"] == r["n_steps"]).mean() > 0.999
+    assert np.corrcoef(a["mcE"], r["mcE"])[0, 1] > 0.5
+
+
+def test_normal_deterministic_and_geometry_independent(gsm):
+    w = synth.workload(3, n_bursts=5000, R=16)
+    b = w.bursts()
+    a = run(gsm, b, w.n_states, w.args[0], 16, 9, 4, gsm.GSM_MODE_NORMAL)
+    c = run(gsm, b, w.n_states, w.args[0], 16, 9, 4, gsm.GSM_MODE_NORMAL)
+    assert np.array_equal(a["mcE"].view(np.uint32), c["mcE"].view(np.uint32))
+    assert np.array_equal(a["hist"], c["hist"]) and a["chi2"] == c["chi2"]
+    d = run(gsm, b, w.n_states, w.args[0], 16, 9, 5, gsm.GSM_MODE_NORMAL)   # another epoch: new draws
+    assert not np.array_equal(a["hist"], d["hist"])
+    # the three photon layouts give the same samples (integer window counts, same arithmetic)
+    e = run(gsm, b, w.n_states, w.args[0], 16, 9, 4, gsm.GSM_MODE_NORMAL, no_index=True)
+    f = run(gsm, b, w.n_states, w.args[0], 16, 9, 4, gsm.GSM_MODE_NORMAL, force_raw64=True)
+    assert np.array_equal(a["mcE"].view(np.uint32), e["mcE"].view(np.uint32))
+    assert np.array_equal(a["mcE"].view(np.uint32), f["mcE"].view(np.uint32))
+
+
+def test_normal_additive_over_burst_shards(gsm):
+    """Burst-split sharding in normal mode: draws are keyed by the global burst id, so the sum of
+    the shard histograms equals the single-device histogram bin for bin."""
+    from gsmfretda_b200 import sharding
+    w = synth.workload(2, n_bursts=6000, R=32)
+    b = w.bursts()
+    full = run(gsm, b, w.n_states, w.args[0], 32, 3, 2, gsm.GSM_MODE_NORMAL, keep=False)
+    tot = np.zeros_like(full["hist"])
+    for (b0, b1) in sharding.split_bursts(b.ph_count, 3):
+        with gsm.Mc(0, 1) as mc:
+            mc.set_reSampleTimes(32); mc.set_seed(3); mc.set_hist(NB, LEFT_PAD)
+            mc.set_mode(gsm.GSM_MODE_NORMAL)
+            mc.init_bursts(b.slice(b0, b1), g_offset=b0)
+            _, h = mc.evaluate(w.n_states, w.args[0], sid=0, epoch=2)
+            tot += h
+    assert np.array_equal(tot, full["hist"])
+
+
+def test_normal_batch_matches_single(gsm):
+    w = synth.workload(4, n_bursts=3000, R=16, P=5)
+    b = w.bursts()
+    with gsm.Mc(0, 1) as mc:
+        mc.set_reSampleTimes(16); mc.set_seed(12); mc.set_hist(NB, LEFT_PAD)
+        mc.set_mode(gsm.GSM_MODE_NORMAL)
+        mc.init_bursts(b)
+        mc.set_epoch(0, 40)
+        mc.run_batch(b.n_bursts, 0, w.n_states, w.args)
+        mc.sync(0)
+        chi2v = mc.chi2v(0).copy()
+        hists = [mc.hist(0, p).copy() for p in range(w.P)]
+        singles = []
+        for p in range(w.P):
+            c, h = mc.evaluate(w.n_states, w.args[p], sid=0, epoch=40 + p)
+            singles.append((c, h.copy()))
+    for p in range(w.P):
+        assert np.array_equal(hists[p], singles[p][1])
+        assert np.float32(chi2v[p]) == np.float32(singles[p][0])
+
+
+def test_normal_edge_cases(gsm, oracle):
+    """empty / zero-duration / one-photon bursts and BTPE-sized windows do not break the mode."""
+    from helpers import load_golden
+    for name in ("edge_mixed_p0", "edge_far_ticks_p0"):
+        b, d = load_golden(name)
+        n = int(d["n"]); R = int(d["R"])
+        g = run(gsm, b, n, d["args"], R, 5, 1, gsm.GSM_MODE_NORMAL)
+        assert g["flags"] == 0
+        assert int(g["hist"].sum()) == b.n_bursts * R
+        assert np.array_equal(g["hist"], oracle.hist(g["mcE"], NB))
+
+
+def test_normal_btpe_window(gsm, oracle):
+    """One long static burst whose single window holds hundreds of photons of one channel:
+    n*p > 30 takes the BTPE fall-back; the mean acceptor count must match the replay mode."""
+    rng = np.random.default_rng(3)
+    B, ph = 4000, 400
+    start = (np.arange(B, dtype=np.int64) * 400000 + 1000)
+    dur = np.full(B, 200000, np.int64)
+    t = np.sort(rng.integers(1, 199999, size=(B, ph)), axis=1) + start[:, None]
+    ad = t.copy().reshape(-1)                       # acceptor photons only: sticky flags never set both
+    b = synth.Bursts(start=start, stop=start + dur, istart=np.arange(B, dtype=np.int64) * ph,
+                     ph_count=np.full(B, ph, np.int32), T=(dur * 1.25e-8).astype(np.float32),
+                     burst_ad=ad, burst_dd=np.zeros_like(ad), SgDivSr=np.full(B, 0.5, np.float32))
+    args = synth.pack_args([0.4, 0.6], [1e-3, 1e-3], [1.0, 1.0])
+    a = run(gsm, b, 2, args, 8, 21, 1, gsm.GSM_MODE_NORMAL)
+    r = run(gsm, b, 2, args, 8, 22, 1, gsm.GSM_MODE_REPLAY)
+    assert a["flags"] == 0 and r["flags"] == 0
+    se = r["sum_ai"].std() / np.sqrt(r["sum_ai"].size)
+    assert r["sum_ai"].mean() > 30
+    assert abs(a["sum_ai"].mean() - r["sum_ai"].mean()) < 6 * se
+    D, p = ks(a["mcE"], r["mcE"])
+    assert p > 0.01, (D, p)
