@@ -124,6 +124,7 @@ struct gsm_ctx {
     int32_t* d_pk = nullptr;
     int32_t* d_pm = nullptr;
     uint32_t* d_nx = nullptr;
+    uint32_t* d_cw = nullptr;
     int64_t* d_ad = nullptr; int64_t* d_dd = nullptr;
     float* d_sg = nullptr;
     float* d_ohist = nullptr;
@@ -347,7 +348,7 @@ void gsm_destroy(gsm_ctx* c)
         if (s.ev1) cudaEventDestroy(s.ev1);
         if (s.stream) cudaStreamDestroy(s.stream);
     }
-    cudaFree(c->d_bursts); cudaFree(c->d_pk); cudaFree(c->d_pm); cudaFree(c->d_nx);
+    cudaFree(c->d_bursts); cudaFree(c->d_pk); cudaFree(c->d_pm); cudaFree(c->d_nx); cudaFree(c->d_cw);
     cudaFree(c->d_ad); cudaFree(c->d_dd);
     cudaFree(c->d_sg); cudaFree(c->d_ohist);
     cudaGetLastError();
@@ -452,13 +453,14 @@ int gsm_init_data(gsm_ctx* c, int64_t B, const int64_t* istart, const int64_t* s
             if (lam > max_lambda) max_lambda = lam;
         }
     }
+    if (pk_total >= (1ll << 34)) return fail(GSM_ERANGE, "%lld photon words: the packed offset covers 2^34", (long long)pk_total);
     if (with_bg && !(max_lambda < 900.0))
         return fail(GSM_ERANGE, "background mean %g per burst: the Poisson draw contract covers lambda < 1000", max_lambda);
     CK(cudaSetDevice(c->devid));
     for (Slot& s : c->slots) CK(cudaStreamSynchronize(s.stream));
-    cudaFree(c->d_bursts); cudaFree(c->d_pk); cudaFree(c->d_pm); cudaFree(c->d_nx);
+    cudaFree(c->d_bursts); cudaFree(c->d_pk); cudaFree(c->d_pm); cudaFree(c->d_nx); cudaFree(c->d_cw);
     cudaFree(c->d_ad); cudaFree(c->d_dd); cudaFree(c->d_sg);
-    c->d_bursts = nullptr; c->d_pk = nullptr; c->d_pm = nullptr; c->d_nx = nullptr;
+    c->d_bursts = nullptr; c->d_pk = nullptr; c->d_pm = nullptr; c->d_nx = nullptr; c->d_cw = nullptr;
     c->d_ad = nullptr; c->d_dd = nullptr; c->d_sg = nullptr;
     c->inited = false;
 
@@ -504,7 +506,8 @@ int gsm_init_data(gsm_ctx* c, int64_t B, const int64_t* istart, const int64_t* s
         if (indexed) {
             CKT(cudaMalloc((void**)&c->d_pm, words * 4));
             CKT(cudaMalloc((void**)&c->d_nx, words * 4));
-            pa.pm = c->d_pm; pa.nx = c->d_nx;
+            CKT(cudaMalloc((void**)&c->d_cw, words * 4));
+            pa.pm = c->d_pm; pa.nx = c->d_nx; pa.cw = c->d_cw;
         }
         CKT(launch_pack(pa, 0));
         c->launches += (B ? (indexed ? 2 : 1) : 0);
@@ -512,12 +515,12 @@ int gsm_init_data(gsm_ctx* c, int64_t B, const int64_t* istart, const int64_t* s
         CKT(cudaMemcpy(&bad, d_bad, 4, cudaMemcpyDeviceToHost));
         if (bad) {  // ticks too far from their burst start for 30 bits: keep the raw layout
             packed = false; indexed = false;
-            cudaFree(c->d_pk); cudaFree(c->d_pm); cudaFree(c->d_nx);
-            c->d_pk = nullptr; c->d_pm = nullptr; c->d_nx = nullptr;
+            cudaFree(c->d_pk); cudaFree(c->d_pm); cudaFree(c->d_nx); cudaFree(c->d_cw);
+            c->d_pk = nullptr; c->d_pm = nullptr; c->d_nx = nullptr; c->d_cw = nullptr;
         }
     }
     if (!packed) {
-        pa.pk = nullptr; pa.pm = nullptr; pa.nx = nullptr;
+        pa.pk = nullptr; pa.pm = nullptr; pa.nx = nullptr; pa.cw = nullptr;
         CKT(launch_pack(pa, 0));
         c->launches += (B ? 1 : 0);
     } else {
@@ -638,7 +641,7 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
     if (r) return r;
     const int nbp = c->nb + 2;
     EvalArgs a{};
-    a.bursts = c->d_bursts; a.pk = c->d_pk; a.pm = c->d_pm; a.nx = c->d_nx; a.ad = c->d_ad; a.dd = c->d_dd;
+    a.bursts = c->d_bursts; a.pk = c->d_pk; a.pm = c->d_pm; a.nx = c->d_nx; a.cw = c->d_cw; a.ad = c->d_ad; a.dd = c->d_dd;
     a.params = s.d_params; a.ohist = c->d_ohist;
     a.whist = s.d_whist;
     a.hist_out = res_hist(s.d_res);

@@ -64,6 +64,10 @@ __device__ __forceinline__ void stage_params(SmemParams& sp, const ParamRaw* __r
 // first index whose running sum exceeds pv, else m-1 (role of drawDisIdx, gen_rand.cuh:35-50)
 __device__ __forceinline__ int pick(const float* cum, int m, float pv)
 {
+    // m is warp-uniform (one parameter vector per warp): the small cases skip the loop
+    if (m <= 1) return 0;
+    if (m == 2) return cum[0] > pv ? 0 : 1;
+    if (m == 3) return cum[0] > pv ? 0 : (cum[1] > pv ? 1 : 2);
     int r = m - 1;
     for (int i = m - 2; i >= 0; --i)
         if (cum[i] > pv) r = i;
@@ -83,12 +87,12 @@ struct Lane {
     // burst record (stop and, in the raw layout, the photon offset are re-read when needed)
     int64_t start;
     uint32_t off4;      // first photon of the burst in the packed stream, in units of 4 words
+    uint32_t scale;     // cell index scale of the burst (indexed layout)
     float T;
     int ph;
     // walk state
     Xor128 xs;          // replay mode only
     float F, acc, spent;
-    int sum_ai;
     int64_t bin0;
     int first, si;
     uint32_t step;
@@ -105,6 +109,16 @@ __device__ __forceinline__ int64_t lane_off(const EvalArgs& a, const Lane& L)
     if (kPacked) return (int64_t)L.off4 << 2;
     return __ldg(&a.bursts[a.b0 + L.bl].off);
 }
+
+// warp-uniform bookkeeping of the persistent loop (one per warp, in shared memory)
+struct WarpCtl {
+    unsigned long long pend_item;   // a fetched chunk of another vector waits for the lanes to drain
+    uint32_t c_bl, c_rep;           // next unassigned sample of the warp's chunk = (burst, repeat)
+    int c_cnt;                      // samples left in the chunk
+    int cur_p;                      // vector whose parameters / histogram this warp holds
+    uint32_t epoch;
+    int have_pending, exhausted;
+};
 
 struct Window {
     int end;        // index of the closing photon; >= ph: the window saw no photon at all
@@ -142,24 +156,29 @@ __device__ __forceinline__ Window scan_linear(const EvalArgs& a, const Lane& L, 
     return w;
 }
 
-// Same result in O(log ph): the closing photon by binary search over the running maximum of
-// the photon words, the counts from the distance to the next acceptor / donor photon.
-// Exact whenever no photon before `first` already reaches the new edge; otherwise (a window
-// edge that moved backwards, unsorted ticks) the photon-by-photon scan decides.
+// Same result in O(1) expected: the cell index brackets the closing photon — photons in cells
+// below cell(thr) are before the edge, photons in cells above it are past it — a binary search
+// over the running maximum inside the bracket (0 or 1 photons on average) finishes it, and the
+// counts follow from the distance to the next acceptor / donor photon.  Exact whenever no photon
+// before `first` already reaches the new edge; otherwise (a window edge that moved backwards,
+// unsorted ticks) the photon-by-photon scan decides.
 __device__ __forceinline__ Window scan_indexed(const EvalArgs& a, const Lane& L, int64_t bin1, int thr)
 {
     if (L.first >= L.ph) return Window{L.ph, 0, 0};
     const int64_t off = lane_off<true>(a, L);
+    const uint32_t nx = __ldg(a.nx + off + L.first);   // independent of the edge: issued first
+    const int Q = ((L.ph + 3) & ~3) - 1;
+    const uint32_t cw = __ldg(a.cw + off + cell_of(thr, L.scale, Q));
+    int lo = (int)(cw & 0xffffu), hi = (int)(cw >> 16);
     const int32_t* __restrict__ pm = a.pm + off;
-    if (L.first > 0 && __ldg(pm + L.first - 1) >= thr) return scan_linear<true>(a, L, bin1, thr);
-    int lo = L.first, hi = L.ph - 1;  // the last photon closes any window that reaches it
     while (lo < hi) {
-        int mid = (lo + hi) >> 1;
+        const int mid = (lo + hi) >> 1;
         if (__ldg(pm + mid) >= thr) hi = mid;
         else lo = mid + 1;
     }
+    if (lo < L.first) return scan_linear<true>(a, L, bin1, thr);
+    lo = lo < L.ph - 1 ? lo : L.ph - 1;                // the last photon closes any window that reaches it
     Window w{lo, 0, 0};
-    const uint32_t nx = __ldg(a.nx + off + L.first);
     const int ia = L.first + (int)(nx & 0xffffu);  // next acceptor photon at or after `first`
     const int id = L.first + (int)(nx >> 16);      // next donor photon
     if (ia < id) {
@@ -185,17 +204,16 @@ __device__ __forceinline__ void lane_begin(Lane& L, const SmemParams& sp, const 
     L.start = ((int64_t)(uint32_t)r0.y << 32) | (uint32_t)r0.x;
     L.T = __int_as_float(r1.x);
     L.ph = r1.y;
-    L.off4 = ((uint32_t)r1.z >> 2) | ((uint32_t)r1.w << 30);
-    const u32x4 sd = philox4x32_10(lane_g(a, L), rep, 0u, kSlotSeed, a.seed, epoch);
+    L.off4 = (uint32_t)r1.z;      // packed layouts; the raw layout re-reads its 64-bit offset
+    L.scale = (uint32_t)r1.w;
     L.si = 0;
-    if (kFast) {
-        // normal mode: x0 is the initial-state uniform; the binomial draws on the step words
-        L.si = pick(sp.cumP, sp.n, u01(sd.x));
-    } else {
+    if (!kFast) {
+        // replay mode: the binomial stream of the sample (draw contract); the
+        // normal mode needs no per-sample block, its draws all come from the step blocks
+        const u32x4 sd = philox4x32_10(lane_g(a, L), rep, 0u, kSlotSeed, a.seed, epoch);
         L.xs.seed((uint64_t)sd.x | ((uint64_t)sd.y << 32));
     }
     L.F = 0.0f; L.acc = 0.0f; L.spent = 0.0f;
-    L.sum_ai = 0;
     L.bin0 = L.start;
     L.first = 0;
     L.step = 0;
@@ -208,7 +226,13 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
     const int n = sp.n;
     const uint32_t g = lane_g(a, L);
     const u32x4 w = philox4x32_10(g, L.rep, L.step, kSlotStep, a.seed, epoch);
-    if (!kFast && L.step == 0) L.si = pick(sp.cumP, n, u01(w.w));
+    if (L.step == 0) {
+        // initial state (mc.cu:110).  Replay: word 3 of the step-0 block (draw contract).  Normal:
+        // the low bytes of the four words — the uniforms of this block are built from the top 24
+        // bits of each word, so those 32 bits are an independent word that costs no Philox call
+        const uint32_t iw = kFast ? ((w.x & 0xffu) | ((w.y & 0xffu) << 8) | ((w.z & 0xffu) << 16) | (w.w << 24)) : w.w;
+        L.si = pick(sp.cumP, n, u01(iw));
+    }
     const int si = L.si;
     int sj = pick(sp.cumJ[si], n - 1, u01(w.x));
     if (sj >= si) ++sj;
@@ -280,7 +304,6 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
         }
     }
     L.acc += (float)ai;
-    L.sum_ai += ai;
     L.bin0 = bin1;
     L.si = sj;
     L.step++;
@@ -345,6 +368,7 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
     __shared__ SmemParams s_params[kWarps];
     extern __shared__ unsigned int s_hist_all[];  // [kWarps][nbp]
     __shared__ int s_last;
+    __shared__ WarpCtl s_ctl[kWarps];
 
     const int lane = threadIdx.x & 31;
     const int wid = threadIdx.x >> 5;
@@ -365,14 +389,14 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
     const bool smallR = a.R < (1 << 15);
     const uint32_t magicR = smallR ? (uint32_t)((0x100000000ull + (uint32_t)a.R - 1u) / (uint32_t)a.R) : 0u;
 
-    int cur_p = -1;           // vector whose parameters / histogram this warp holds
-    uint32_t epoch = 0;
-    // the warp's chunk: next unassigned sample = (burst c_bl, repeat c_rep), c_cnt samples left
-    uint32_t c_bl = 0, c_rep = 0;
-    int c_cnt = 0;
-    bool have_pending = false;  // a fetched chunk of another vector waits for the lanes to drain
-    unsigned long long pend_item = 0;
-    bool exhausted = false;
+    // warp-uniform bookkeeping lives in shared memory (volatile: every access is a broadcast
+    // LDS / a lane-0 STS), which keeps it out of the per-thread register budget
+    volatile WarpCtl& wc = s_ctl[wid];
+    if (lane == 0) {
+        wc.cur_p = -1; wc.epoch = 0u; wc.c_bl = 0u; wc.c_rep = 0u; wc.c_cnt = 0;
+        wc.have_pending = 0; wc.exhausted = 0; wc.pend_item = 0ull;
+    }
+    __syncwarp();
 
     Lane L;
     bool active = false;
@@ -382,26 +406,31 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
         for (;;) {
             const unsigned need = __ballot_sync(0xffffffffu, !active);
             if (need == 0u) break;
+            int c_cnt = wc.c_cnt;
             if (c_cnt <= 0) {
                 unsigned long long item;
-                if (have_pending) {
+                if (wc.have_pending) {
                     if (need != 0xffffffffu) break;  // lanes of the previous vector still walking
-                    item = pend_item;
+                    item = wc.pend_item;
                 } else {
-                    if (exhausted) break;
+                    if (wc.exhausted) break;
                     item = 0;
                     if (lane == 0) item = atomicAdd(a.counters + 0, 1ull);
                     item = __shfl_sync(0xffffffffu, item, 0);
                     if (item >= items) {
-                        exhausted = true;
+                        __syncwarp();
+                        if (lane == 0) wc.exhausted = 1;
+                        __syncwarp();
                         break;
                     }
                 }
                 const int p = small ? (int)((uint32_t)item / (uint32_t)chunks_per_p) : (int)(item / chunks_per_p);
+                const int cur_p = wc.cur_p;
                 if (p != cur_p) {
                     if (need != 0xffffffffu) {   // park the chunk until every lane has drained
-                        have_pending = true;
-                        pend_item = item;
+                        __syncwarp();
+                        if (lane == 0) { wc.have_pending = 1; wc.pend_item = item; }
+                        __syncwarp();
                         break;
                     }
                     // all lanes idle: switch vector
@@ -415,41 +444,47 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
                     }
                     __syncwarp();
                     stage_params(sp, a.params + p, lane);
+                    if (lane == 0) { wc.cur_p = p; wc.epoch = a.epoch0 + (uint32_t)p; }
                     __syncwarp();
-                    cur_p = p;
-                    epoch = a.epoch0 + (uint32_t)cur_p;
                 }
-                have_pending = false;
                 const unsigned long long c = item - (unsigned long long)p * chunks_per_p;
                 const int64_t t0 = (int64_t)c * kChunk;
                 const int64_t left = per_p - t0;
-                c_cnt = left < kChunk ? (int)left : kChunk;
                 const int64_t bl0 = small ? (int64_t)((uint32_t)t0 / (uint32_t)a.R) : t0 / a.R;
-                c_bl = (uint32_t)bl0;
-                c_rep = (uint32_t)(t0 - bl0 * a.R);
+                __syncwarp();
+                if (lane == 0) {
+                    wc.have_pending = 0;
+                    wc.c_cnt = left < kChunk ? (int)left : kChunk;
+                    wc.c_bl = (uint32_t)bl0;
+                    wc.c_rep = (uint32_t)(t0 - bl0 * a.R);
+                }
+                __syncwarp();
                 continue;
             }
+            const uint32_t c_bl = wc.c_bl, c_rep = wc.c_rep;
             const int rank = __popc(need & lt_mask);
             const bool take = !active && rank < c_cnt;
             const int want = __popc(need);
             if (take) {
                 const uint32_t x = c_rep + (uint32_t)rank;
                 const uint32_t q = smallR ? __umulhi(x, magicR) : x / (uint32_t)a.R;
-                lane_begin<kFast>(L, sp, a, c_bl + q, x - q * (uint32_t)a.R, epoch);
+                lane_begin<kFast>(L, sp, a, c_bl + q, x - q * (uint32_t)a.R, wc.epoch);
                 active = true;
             }
-            {
+            __syncwarp();
+            if (lane == 0) {
                 const int adv = want < c_cnt ? want : c_cnt;
-                c_cnt -= adv;
                 const uint32_t x = c_rep + (uint32_t)adv;
                 const uint32_t q = smallR ? __umulhi(x, magicR) : x / (uint32_t)a.R;
-                c_bl += q;
-                c_rep = x - q * (uint32_t)a.R;
+                wc.c_cnt = c_cnt - adv;
+                wc.c_bl = c_bl + q;
+                wc.c_rep = x - q * (uint32_t)a.R;
             }
+            __syncwarp();
             // a burst of zero duration never enters the reference's while loop: E = 0
             const bool dead = take && !(L.T > 0.0f);
             if (dead) {
-                const size_t oi = (size_t)cur_p * (size_t)per_p + (size_t)L.bl * (size_t)a.R + L.rep;
+                const size_t oi = (size_t)wc.cur_p * (size_t)per_p + (size_t)L.bl * (size_t)a.R + L.rep;
                 if (a.mcE) a.mcE[oi] = 0.0f;
                 if (a.sum_ai) a.sum_ai[oi] = 0;
                 if (a.n_steps) a.n_steps[oi] = 0;
@@ -458,24 +493,26 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
             }
         }
         if (__ballot_sync(0xffffffffu, active) == 0u) {
-            if (exhausted && !have_pending) break;
+            if (wc.exhausted && !wc.have_pending) break;
             continue;
         }
 
         // ---- one dwell window for every active lane -------------------------------------
         if (active) {
-            lane_step<kLayout, kBg, kFast>(L, sp, a, epoch);
+            lane_step<kLayout, kBg, kFast>(L, sp, a, wc.epoch);
             bool fin = !(L.T > L.spent);
             if (!fin && L.step >= kStepCap) {
                 atomicOr(a.counters + 2, 1ull);
                 fin = true;
             }
             if (fin) {
-                const float e = (L.F > 0.0f) ? (kFast ? __fdividef(L.acc, L.F) : L.acc / L.F) : 0.0f;
+                // IEEE division in both modes: E takes few distinct values (small integer
+                // counts), so a 1-ulp difference would move whole atoms of the distribution
+                const float e = (L.F > 0.0f) ? __fdiv_rn(L.acc, L.F) : 0.0f;
                 if (a.mcE || a.sum_ai || a.n_steps) {
-                    const size_t oi = (size_t)cur_p * (size_t)per_p + (size_t)L.bl * (size_t)a.R + L.rep;
+                    const size_t oi = (size_t)wc.cur_p * (size_t)per_p + (size_t)L.bl * (size_t)a.R + L.rep;
                     if (a.mcE) a.mcE[oi] = e;
-                    if (a.sum_ai) a.sum_ai[oi] = (long long)L.sum_ai;
+                    if (a.sum_ai) a.sum_ai[oi] = (long long)L.acc;   // integer-valued, exact below 2^24
                     if (a.n_steps) a.n_steps[oi] = (int32_t)L.step;
                 }
                 // warp-aggregated add: one shared-memory atomic per distinct bin among the
@@ -489,6 +526,7 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
         }
         __syncwarp();
     }
+    const int cur_p = wc.cur_p;
 
     // queue drained: flush this warp's bins, then the last block to arrive finalises
     if (cur_p >= 0) {

@@ -43,7 +43,12 @@ __global__ void pda_pack_kernel(const PackArgs a)
         r.stop = a.stop[b];
         r.T = a.T[b];
         r.ph = ph;
-        r.off = a.pk ? a.poff[b] : is;
+        if (a.pk) {
+            r.off4 = (uint32_t)(a.poff[b] >> 2);
+            r.scale = 0u;   // set by pda_index_kernel
+        } else {
+            r.off = is;
+        }
         a.bursts[b] = r;
     }
     if (!a.pk) return;
@@ -68,8 +73,11 @@ __global__ void pda_pack_kernel(const PackArgs a)
     if (bad) atomicAdd(a.bad, bad);
 }
 
-// per-burst index over the packed words: running maximum (binary-searchable window edge) and
-// distance to the next acceptor / donor photon (window counts in O(1)); one thread per burst
+// per-burst index over the packed words: running maximum (searchable window edge), distance
+// to the next acceptor / donor photon (window counts in O(1)) and a cell index — the word range
+// of the burst cut into Q = padded-1 cells by a monotone map, cw[c] = photons in cells below c
+// (low half) and below c+1 (high half) — that brackets the closing photon of a window with one
+// load; one thread per burst
 __global__ void pda_index_kernel(const PackArgs a)
 {
     const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -91,6 +99,25 @@ __global__ void pda_index_kernel(const PackArgs a)
         if (f & 1) nd = i;
         a.nx[po + i] = (uint32_t)(na - i) | ((uint32_t)(nd - i) << 16);
     }
+    if (!a.cw || ph <= 0) return;
+    const int Q = padded - 1;
+    const uint32_t maxkey = (uint32_t)(m > 0 ? m : 0);
+    const unsigned long long s64 = ((unsigned long long)Q << 32) / ((unsigned long long)maxkey + 1ull);
+    const uint32_t scale = s64 > 0xffffffffull ? 0xffffffffu : (uint32_t)s64;
+    a.bursts[b].scale = scale;
+    // below[c] for c = 0..Q, written pairwise into cw[c] = below[c] | below[c+1] << 16
+    int c_prev = 0;          // below[0..c_prev] are known
+    uint32_t lo = 0u;        // below[c_prev]
+    for (int i = 0; i <= ph; ++i) {
+        int c = Q;           // sentinel after the last photon: every remaining cell holds ph below
+        if (i < ph) c = cell_of(a.pm[po + i], scale, Q);
+        while (c_prev < c) { // below[c_prev + 1] = i
+            a.cw[po + c_prev] = lo | ((uint32_t)i << 16);
+            lo = (uint32_t)i;
+            ++c_prev;
+        }
+    }
+    a.cw[po + Q] = lo | (lo << 16);
 }
 
 // boost regular-axis histogram of a float array (observed SgDivSr histogram,

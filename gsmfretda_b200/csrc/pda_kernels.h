@@ -15,7 +15,13 @@ struct __align__(16) BurstRec {
     int64_t stop;
     float T;
     int32_t ph;
-    int64_t off;  // first photon: index into the packed stream (multiple of 4) or into burst_ad/dd
+    union {
+        int64_t off;          // raw layout: first photon in burst_ad / burst_dd
+        struct {
+            uint32_t off4;    // packed layouts: first photon word / 4 (bursts are 16-byte aligned)
+            uint32_t scale;   // cell index: cell(word) = min(Q-1, umulhi(max(word,0), scale))
+        };
+    };
 };
 static_assert(sizeof(BurstRec) == 32, "BurstRec must be 32 bytes");
 
@@ -35,6 +41,7 @@ struct EvalArgs {
     const int32_t* pk;         // packed photons, (rel_tick << 2) | acceptor << 1 | donor ; or null
     const int32_t* pm;         // running maximum of pk & ~3 inside each burst ; or null
     const uint32_t* nx;        // distance to the next acceptor (low 16) / donor (high 16) photon ; or null
+    const uint32_t* cw;        // cell index: photons in cells below c (low 16) / below c+1 (high 16) ; or null
     const int64_t* ad;         // raw burst_ad / burst_dd (fallback layout); or null
     const int64_t* dd;
     const ParamRaw* params;    // [P]
@@ -85,6 +92,7 @@ struct PackArgs {
     int32_t* pk;             // out, may be null (raw layout: bursts only)
     int32_t* pm;             // out, may be null (no index)
     uint32_t* nx;            // out, may be null
+    uint32_t* cw;            // out, may be null
     unsigned int* bad;       // out: number of photons that do not fit the packed layout
     int64_t B;
 };

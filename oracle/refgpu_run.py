@@ -44,11 +44,20 @@ def main():
     saved = os.dup(1)
     os.dup2(devnull, 1)          # the reference prints device info and "blockSize" on stdout
     try:
+        def stage(msg, t=[time.perf_counter()]):
+            now = time.perf_counter()
+            print("[refgpu_run] %s (+%.2f s)" % (msg, now - t[0]), file=sys.stderr, flush=True)
+            t[0] = now
         m = oracle_py.RefGpu(0, 1)
+        stage("created")
         R = m.set_reSampleTimes(a.repeats)
         m.init_bursts(b)
+        stage("init_data_gpu done, R=%d" % R)
         arg = w.args[a.pvec]
-        out = [m.evaluate(w.n_states, arg) for _ in range(a.evals)]
+        out = []
+        for i in range(a.evals):
+            out.append(m.evaluate(w.n_states, arg))
+            stage("evaluation %d done" % i)
         line = None
         if a.time > 0:
             m.time(w.n_states, arg, 3)

@@ -35,14 +35,32 @@ def ks(a, b):
     return float(r.statistic), float(r.pvalue)
 
 
+def homogeneity(a, b, min_count=20):
+    """two-sample chi-square test of two histograms on the bins whose pooled count >= min_count"""
+    from scipy import stats
+    a = a[:NB].astype(np.float64); b = b[:NB].astype(np.float64)
+    m = (a + b) >= min_count
+    a, b = a[m], b[m]
+    ka, kb = np.sqrt(b.sum() / a.sum()), np.sqrt(a.sum() / b.sum())
+    st = float((((ka * a - kb * b) ** 2) / (a + b)).sum())
+    return st, float(stats.chi2.sf(st, int(m.sum()) - 1))
+
+
 # (cfg, bursts, R): about 1e6 samples per side
 CASES = [(1, 16000, 64), (2, 10000, 100), (3, 60000, 16), (5, 120000, 8)]
+EPOCHS = 6      # evaluations per side for the chi-square comparison
 
 
 @pytest.mark.parametrize("cfg,nb,R", CASES)
 def test_normal_vs_oracle_replay_statistics(gsm, oracle, cfg, nb, R):
+    """KS p > 0.01 on E, histograms homogeneous at p > 0.01, reduced chi-square within 1 % or
+    within its own Monte-Carlo error.  The reference's chi-square divides by the model count, so
+    sparse bins dominate it: between two independent runs of the ORACLE it already moves by
+    1 % (cfg 2, 3), 4 % (cfg 5) and 27 % (cfg 1) at these sizes (tools/normal_diag.py), hence
+    the comparison of means over EPOCHS evaluations with the measured standard errors."""
     w = synth.workload(cfg, n_bursts=nb, R=R)
     b = w.bursts()
+    ohist = oracle.observed_hist(b, NB)
     g = run(gsm, b, w.n_states, w.args[0], R, seed=101, epoch=1, mode=gsm.GSM_MODE_NORMAL)
     o = oracle.eval(b, w.n_states, w.args[0], R, 202, 1)            # independent draws
     assert g["flags"] == 0
@@ -51,9 +69,8 @@ def test_normal_vs_oracle_replay_statistics(gsm, oracle, cfg, nb, R):
     D, p = ks(g["mcE"], o["mcE"])
     assert p > 0.01, (D, p)
     oh = oracle.hist(o["mcE"], NB)
-    ohist = oracle.observed_hist(b, NB)
-    c_o = oracle.chi2(ohist, oh, NB, R, LEFT_PAD, w.n_states)
-    assert abs(g["chi2"] - c_o) / c_o < 0.01, (g["chi2"], c_o)
+    st, ph = homogeneity(g["hist"], oh)
+    assert ph > 0.01, (st, ph)
     # the fused histogram is the histogram of the per-sample values it returns
     assert np.array_equal(g["hist"], oracle.hist(g["mcE"], NB))
     # integer bookkeeping: mean acceptor counts and dwell steps agree to MC error
@@ -61,19 +78,53 @@ def test_normal_vs_oracle_replay_statistics(gsm, oracle, cfg, nb, R):
     assert abs(g["sum_ai"].mean() - o["sum_ai"].mean()) < 6 * se + 1e-9
     se = o["n_steps"].std() / np.sqrt(o["n_steps"].size)
     assert abs(g["n_steps"].mean() - o["n_steps"].mean()) < 6 * se + 1e-9
+    # reduced chi-square: mean over EPOCHS evaluations on both sides
+    c_o = [oracle.chi2(ohist, oh, NB, R, LEFT_PAD, w.n_states)]
+    for s in range(1, EPOCHS):
+        e = oracle.eval(b, w.n_states, w.args[0], R, 202 + 1000 * s, 1)["mcE"]
+        c_o.append(oracle.chi2(ohist, oracle.hist(e, NB), NB, R, LEFT_PAD, w.n_states))
+    c_g = [g["chi2"]]
+    with gsm.Mc(0, 1) as mc:
+        mc.set_reSampleTimes(R); mc.set_seed(101); mc.set_hist(NB, LEFT_PAD)
+        mc.set_mode(gsm.GSM_MODE_NORMAL)
+        mc.init_bursts(b)
+        for ep in range(2, EPOCHS + 1):
+            c_g.append(mc.evaluate(w.n_states, w.args[0], sid=0, epoch=ep)[0])
+    c_o, c_g = np.asarray(c_o, np.float64), np.asarray(c_g, np.float64)
+    se = np.sqrt(c_o.var(ddof=1) / c_o.size + c_g.var(ddof=1) / c_g.size)
+    assert abs(c_g.mean() - c_o.mean()) < max(0.01 * c_o.mean(), 4.0 * se), (c_g, c_o)
+
+
+def test_normal_chi2_within_one_percent_of_replay_full_size(gsm):
+    """BASELINE config 2 at full size (1e5 bursts x 100 repeats = 1e7 samples per evaluation),
+    where the Monte-Carlo error of the reduced chi-square is small enough for the north-star
+    bar to be read literally: mean chi-square of the normal mode within 1 % of the replay
+    mode (= the oracle's arithmetic, bit for bit), independent draws on the two sides."""
+    w = synth.workload(2)
+    b = w.bursts()
+    means = {}
+    for mode, seed in ((gsm.GSM_MODE_NORMAL, 11), (gsm.GSM_MODE_REPLAY, 22)):
+        with gsm.Mc(0, 1) as mc:
+            mc.set_reSampleTimes(w.R); mc.set_seed(seed); mc.set_hist(NB, LEFT_PAD)
+            mc.set_mode(mode)
+            mc.init_bursts(b)
+            means[mode] = np.mean([mc.evaluate(w.n_states, w.args[0], sid=0, epoch=ep)[0] for ep in range(1, 9)])
+    a, r = means[gsm.GSM_MODE_NORMAL], means[gsm.GSM_MODE_REPLAY]
+    assert abs(a - r) / r < 0.01, (a, r)
 
 
 @pytest.mark.parametrize("cfg,nb,R", [(2, 4000, 16), (5, 4000, 4)])
 def test_normal_same_walk_as_replay(gsm, cfg, nb, R):
     """Both modes key Philox the same way, so with the same seed the Markov walk (state picks,
     window edges) is the same up to float rounding of the dwell times: step counts agree on
-    almost every sample, and E is strongly correlated."""
+    almost every sample, and E is correlated (the binomial draws differ)."""
     w = synth.workload(cfg, n_bursts=nb, R=R)
     b = w.bursts()
     a = run(gsm, b, w.n_states, w.args[0], R, 7, 5, gsm.GSM_MODE_NORMAL)
     r = run(gsm, b, w.n_states, w.args[0], R, 7, 5, gsm.GSM_MODE_REPLAY)
     assert (a["n_steps"] == r["n_steps"]).mean() > 0.999
-    assert np.corrcoef(a["mcE"], r["mcE"])[0, 1] > 0.5
+    # same efficiencies per window, independent binomial draws: positively correlated E
+    assert np.corrcoef(a["mcE"], r["mcE"])[0, 1] > 0.2
 
 
 def test_normal_deterministic_and_geometry_independent(gsm):

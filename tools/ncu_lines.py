@@ -8,7 +8,7 @@ rep, so, kern = sys.argv[1], sys.argv[2], sys.argv[3]
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
 tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(so)], cwd=tmp, check=True, capture_output=True)
-cubin = [f for f in os.listdir(tmp) if f.startswith("pda_kernels")][0]
+cubin = next(f for f in sorted(os.listdir(tmp)) if f.endswith(".cubin") and kern in subprocess.run(["cuobjdump", "-elf", os.path.join(tmp, f)], capture_output=True, text=True).stdout)
 dis = subprocess.run(["nvdisasm", "--print-line-info", os.path.join(tmp, cubin)], capture_output=True, text=True).stdout
 lines = dis.split("\n")
 # locate function

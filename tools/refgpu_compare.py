@@ -16,6 +16,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "oracle"))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
 
 
 def ks2(x, y):
@@ -36,6 +37,7 @@ def main():
     ap.add_argument("--bursts", type=int, default=20000)
     ap.add_argument("--repeats", type=int, default=64)
     ap.add_argument("--mode", type=int, default=0, help="gsm mode (0 replay, 1 normal)")
+    ap.add_argument("--timeout", type=float, default=150.0, help="seconds allowed for one reference run")
     a = ap.parse_args()
     import oracle_py
     from gsmfretda_b200 import capi, synth
@@ -47,7 +49,7 @@ def main():
             out = os.path.join(td, "ref.npz")
             subprocess.run([sys.executable, os.path.join(ROOT, "oracle", "refgpu_run.py"), "--cfg", str(cfg),
                             "--bursts", str(a.bursts), "--repeats", str(a.repeats), "--evals", "2",
-                            "--out", out], check=True)
+                            "--out", out], check=True, timeout=a.timeout)
             d = np.load(out)
             ref = d["mcE"]
             R = int(d["R"])
@@ -70,6 +72,10 @@ def main():
                "chi2_ours": [chi(ours[0]), chi(ours[1])], "chi2_ref": [chi(ref[0]), chi(ref[1])],
                "mean_ours": float(ours[0].mean()), "mean_ref": float(ref[0].mean()),
                "nan_ref": int(np.isnan(ref[0]).sum())}
+        from normal_diag import homogeneity
+        res["homog_ours_vs_ref"] = homogeneity(hist200(ours[0]), hist200(ref[0]))
+        res["homog_ref_vs_ref"] = homogeneity(hist200(ref[0]), hist200(ref[1]))
+        res["homog_ours_vs_ours"] = homogeneity(hist200(ours[0]), hist200(ours[1]))
         res["chi2_rel_diff"] = abs(res["chi2_ours"][0] - res["chi2_ref"][0]) / res["chi2_ref"][0]
         print(json.dumps(res), flush=True)
 
