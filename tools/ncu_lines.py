@@ -22,6 +22,12 @@ for l in lines[start + 1:]:
     if m:
         cur = (os.path.basename(m.group(1)), int(m.group(2)))
         continue
+    m = re.match(r'^(\$[\w$.]+):', l)   # helper subroutine placed after the kernel body (no line info)
+    if m:
+        nm = m.group(1)
+        nm = re.sub(r'^\$_ZN.*?\$', '$', nm)
+        cur = ("sub " + nm[:60], 0)
+        continue
     m = re.match(r'\s*/\*([0-9a-f]{4,})\*/\s+(.*?);', l)
     if m:
         addr2line[int(m.group(1), 16)] = (cur, m.group(2))
@@ -49,7 +55,7 @@ for r in rows[hi + 1:]:
 print(f"total warp-inst {tot[0]:,}  thread-inst {tot[1]:,}  samples {tot[2]:,}  avg active {tot[1]/max(1,tot[0]):.2f}")
 src_cache = {}
 def src(key):
-    if not key: return ""
+    if not key or key[1] == 0: return ""
     f, n = key
     for d in ("gsmfretda_b200/csrc",):
         p = os.path.join(os.path.dirname(os.path.abspath(so)), "csrc", f)
@@ -60,5 +66,5 @@ def src(key):
     return ""
 print(f"{'line':28s} {'warp-inst%':>10s} {'samples%':>9s} {'act':>5s} {'#sass':>5s}  source")
 for key, g in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
-    nm = f"{key[0]}:{key[1]}" if key else "?"
+    nm = (f"{key[0]}:{key[1]}" if key[1] else key[0]) if key else "?"
     print(f"{nm:28s} {100*g[0]/tot[0]:10.2f} {100*g[2]/max(1,tot[2]):9.2f} {g[1]/max(1,g[0]):5.1f} {g[3]:5d}  {src(key)}")
