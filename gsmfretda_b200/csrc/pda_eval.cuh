@@ -507,8 +507,10 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
             }
             if (fin) {
                 // IEEE division in both modes: E takes few distinct values (small integer
-                // counts), so a 1-ulp difference would move whole atoms of the distribution
-                const float e = (L.F > 0.0f) ? __fdiv_rn(L.acc, L.F) : 0.0f;
+                // counts), so a 1-ulp difference would move whole atoms of the distribution.
+                // 0 / F = +0 is spelled out: a zero numerator (no acceptor photon drawn — a
+                // large share of the samples) sends the division through its slow path.
+                const float e = (L.F > 0.0f && L.acc != 0.0f) ? __fdiv_rn(L.acc, L.F) : 0.0f;
                 if (a.mcE || a.sum_ai || a.n_steps) {
                     const size_t oi = (size_t)wc.cur_p * (size_t)per_p + (size_t)L.bl * (size_t)a.R + L.rep;
                     if (a.mcE) a.mcE[oi] = e;

@@ -77,7 +77,15 @@ class mc {
         GSM_CHECK_RETURN(rc);
         streamNum = gsm_stream_count(ctx);
         workerNum.store(streamNum);
-        gsm_device_uuid(ctx, gpuuuid);
+        // the reference keeps the 16 raw bytes of the device uuid in gpuuuid (mc.cu:43-48); the C
+        // ABI hands out 32 hex digits
+        char hex[33] = {0};
+        gsm_device_uuid(ctx, hex);
+        for (int i = 0; i < 33; ++i) gpuuuid[i] = 0;
+        for (int i = 0; i < 16 && hex[2 * i] && hex[2 * i + 1]; ++i) {
+            auto nib = [](char c) { return c <= '9' ? c - '0' : (c | 0x20) - 'a' + 10; };
+            gpuuuid[i] = (char)((nib(hex[2 * i]) << 4) | nib(hex[2 * i + 1]));
+        }
         GSM_CHECK_RETURN(gsm_set_seed(ctx, opt.seed));
         GSM_CHECK_RETURN(gsm_set_hist(ctx, opt.fret_hist_num, opt.left_pad));
         GSM_CHECK_RETURN(gsm_set_resample_times(ctx, reSampleTimes));
