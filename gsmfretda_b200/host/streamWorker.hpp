@@ -47,6 +47,7 @@ class streamWorker {
 
     bool host_hist = false;     // true: the reference's host path (hmcE -> histogram -> chi-square)
     int keepalive_every = 60;   // waits of 500 ms between two 'k' messages (streamWorker.cpp:165)
+    bool epoch_from_idx = false;  // draws of an evaluation keyed by the server's params_idx (reproducible)
 
     // boost::histogram regular axis [lv, uv) with binnum bins, inner bins only (role of mkhist +
     // indexed(coverage::inner), streamWorker.cpp:33-38,62-67; bin rule of
@@ -140,6 +141,9 @@ class streamWorker {
                 for (int pi = 0; pi < ps_n; pi++) params[sid][(size_t)pi] = pi < ga.params_size() ? ga.params(pi) : 0.0f;
                 ga_start[sid] = ga.start();
                 ga_stop[sid] = ga.stop();
+                // (a host-side field of the stream slot; this thread holds _m[sid] and the GPU thread
+                // only touches the slot in states 2 and 3)
+                if (epoch_from_idx) gsm_set_epoch(pdamc->handle(), sid, (uint32_t)params_idx + 1u);
                 dataready[sid] = 2;
                 lck.unlock();
                 _cv[sid].notify_one();
