@@ -8,6 +8,9 @@ A "step" is one evaluation of one parameter vector over the whole synthetic burs
 (config 2: 1e5 bursts x 100 repeats = 1e7 burst-samples per GPU).  At N > 1 (torchrun) every
 rank holds its own 1e5-burst shard of one N x 1e5-burst dataset (weak scaling) and each step
 all-reduces the histogram with NCCL before chi-square (burst-split mode).
+--cfg 4 is the GA population: a step is one batch of 1024 parameter vectors over 1e5 bursts x 16
+repeats in ONE launch (gsm_run_batch); at N > 1 the population is split across the ranks with no
+collective (population mode) and the burst data is replicated (strong scaling of the batch).
 
   value     device-timed (CUDA events on the launching stream), inputs resident in HBM
   e2e       the same step through the public API with host buffers: set_nstates/set_params/
@@ -224,17 +227,25 @@ def main():
         torch.cuda.synchronize()
 
     # ---- data: every rank owns one shard of a world x B burst dataset ------------------
-    b = w.bursts(seed=w.seed + 1000 * rank)
+    population = args.cfg == 4
+    # burst-split: every rank its own shard; population: the same bursts on every rank
+    b = w.bursts(seed=w.seed if population else w.seed + 1000 * rank)
     B, R, n = b.n_bursts, w.R, w.n_states
     arg0 = w.args[0]
+    P_job = w.args.shape[0] if population else 1
+    if population:
+        from gsmfretda_b200 import sharding
+        p0, p1 = sharding.split_population(P_job, world)[rank]
+        args_local = np.ascontiguousarray(w.args[p0:p1])
+    P_local = (p1 - p0) if population else 1
     mc = capi.Mc(local_rank, 2)
     mc.set_gpuid()
     mc.set_reSampleTimes(R)
     mc.set_seed(SEED)
     mc.set_hist(NB, LEFT_PAD)
     mc.set_mode(capi.GSM_MODE_NORMAL if args.mode == "normal" else capi.GSM_MODE_REPLAY)
-    mc.init_bursts(b, g_offset=rank * B)
-    if world > 1:
+    mc.init_bursts(b, g_offset=0 if population else rank * B)
+    if world > 1 and not population:
         idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
             idt.copy_(torch.frombuffer(bytearray(capi.comm_unique_id()), dtype=torch.uint8))
@@ -243,19 +254,27 @@ def main():
         oh = torch.from_numpy(mc.observed_hist()).cuda()
         dist.all_reduce(oh)  # counts < 2^24: exact in f32
         mc.set_observed_hist(oh.cpu().numpy())
-    samples_rank = B * R
-    samples_job = samples_rank * world
+    samples_rank = B * R * P_local
+    samples_job = B * R * P_job if population else samples_rank * world
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
     def step_resident():
         flush.zero_()
         torch.cuda.synchronize()
-        mc.run_resident(B, 0)
+        if population:
+            mc.run_batch(B, 0, n, args_local)   # the vectors (612 B each) travel with the launch
+        else:
+            mc.run_resident(B, 0)
         mc.sync(0)
         return mc.elapsed_ms(0)
 
     def step_e2e():
+        if population:
+            mc.run_batch(B, 0, n, args_local)
+            while not mc.streamQuery(0):
+                pass
+            return mc.chi2v(0), mc.hist(0, P_local - 1)
         mc.set_nstates(n, 0)
         mc.set_params(n, 0, arg0)
         Ns = mc.setBurstBd(0, -1, 0)
@@ -266,7 +285,7 @@ def main():
 
     # resident parameters for the device-timed leg
     chi2_first, hist_first = mc.evaluate(n, arg0, sid=0)
-    assert int(hist_first.sum()) == samples_job, (int(hist_first.sum()), samples_job)
+    assert int(hist_first.sum()) == (B * R if population else samples_job), (int(hist_first.sum()), samples_job)
     clocks = ClockSampler(local_rank)
     clocks.start()              # nvidia-smi needs ~0.5 s to come up: start it before the warm-up
     for _ in range(max(args.warmup, 3)):
@@ -292,18 +311,34 @@ def main():
     e2e_s = time.perf_counter() - t0
     clocks.mark_end()
     clk = clocks.stop()
-    assert int(hist_last.sum()) == samples_job
+    assert int(hist_last.sum()) == (B * R if population else samples_job)
+    if population:
+        assert chi2_last.shape[0] == P_local and np.isfinite(chi2_last).all()
+        chi2_last = float(chi2_last[0])
+
+    # the same step in the other arithmetic (replay <-> normal), device-timed, for the record
+    other = "normal" if args.mode == "replay" else "replay"
+    mc.set_mode(capi.GSM_MODE_NORMAL if other == "normal" else capi.GSM_MODE_REPLAY)
+    k_other = max(3, min(args.steps, 50))
+    for _ in range(3):
+        step_resident()
+    barrier()
+    ms_other = float(sum(step_resident() for _ in range(k_other)))
+    barrier()
+
+    # measured issue peak (IMAD / FFMA chains on every SM), right after the timed regions
+    peak_imad, peak_ffma = mc.issue_peak(0), mc.issue_peak(1)
 
     if world > 1:
-        t = torch.tensor([dev_ms, e2e_s, t_wall], dtype=torch.float64, device="cuda")
+        t = torch.tensor([dev_ms, e2e_s, t_wall, ms_other], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dev_ms, e2e_s, t_wall = (float(x) for x in t.cpu())
+        dev_ms, e2e_s, t_wall, ms_other = (float(x) for x in t.cpu())
 
     if rank == 0:
         peak, peak_src, sm_max = measured_peaks()
         ms_per_step = dev_ms / args.steps
         value = samples_job * args.steps / (dev_ms * 1e-3)
-        algo_bytes = b.algorithmic_bytes()
+        algo_bytes = b.algorithmic_bytes() + (612 * P_local if population else 0)
         achieved = algo_bytes / (ms_per_step * 1e-3) / 1e9
         f_clk = (clk.get("sm_mhz") or sm_max) * 1e6
         issue_peak = 148 * 128 * f_clk
@@ -311,23 +346,29 @@ def main():
         out = {
             "metric": "burst-samples/s", "value": value, "unit": "burst-samples/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "higher_is_better": True, "scaling": "strong" if population else "weak", "vs_baseline": None,
             "dtype": ("f32 walk + f64 binomial (replay arithmetic), u32/u64 histogram" if args.mode == "replay"
                       else "f32 (normal mode: hardware lg2/ex2/rcp, f32 binomial inversion), u32/u64 histogram"),
             "mode": args.mode,
             "data": "synthetic",
             "config": {"workload": w.name, "bursts_per_gpu": B, "photons_per_gpu": b.n_photons,
-                       "repeats": R, "states": n, "param_vectors": 1, "hist_bins": NB,
-                       "sharding": "single GPU" if world == 1 else f"burst-split x{world}, NCCL all-reduce of the histogram",
+                       "repeats": R, "states": n, "param_vectors": P_job, "hist_bins": NB,
+                       "sharding": "single GPU" if world == 1 else
+                                   (f"population split x{world}, no collective" if population else
+                                    f"burst-split x{world}, NCCL all-reduce of the histogram"),
                        "l2": "256 MiB buffer written between timed iterations (L2 flush)",
                        "timing": "CUDA events on the launching stream per step, summed; max over ranks",
                        "photon_layout": "packed 4 B/photon" if mc.is_packed() else "raw 16 B/photon"},
-            "param_evals_per_s": args.steps * 1.0 / (dev_ms * 1e-3),
+            "param_evals_per_s": args.steps * P_job / (dev_ms * 1e-3),
+            "other_mode": {"mode": other, "value": samples_job * k_other / (ms_other * 1e-3), "unit": "burst-samples/s",
+                           "ms_per_step": ms_other / k_other, "steps": k_other},
             "wall_s_timed_region": t_wall,
             "e2e": {"value": samples_job * args.steps / e2e_s, "unit": "burst-samples/s",
-                    "h2d_bytes_per_step": 612, "d2h_bytes_per_step": 16 + (NB + 2) * 8 + 4,
+                    "h2d_bytes_per_step": 612 * P_local, "d2h_bytes_per_step": 16 + P_local * ((NB + 2) * 8 + 4),
+                    "param_evals_per_s": args.steps * P_job / e2e_s,
                     "ms_per_step": 1e3 * e2e_s / args.steps,
-                    "api": "Mc.set_nstates/set_params/setBurstBd/run_kernel/streamQuery + chi2()/hist()"},
+                    "api": ("Mc.run_batch/streamQuery + chi2v()/hist()" if population else
+                            "Mc.set_nstates/set_params/setBurstBd/run_kernel/streamQuery + chi2()/hist()")},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
@@ -336,7 +377,9 @@ def main():
             "issue": {"algorithmic_thread_ops_per_sample": ALGO_OPS[args.cfg],
                       "achieved_thread_ops_per_s": per_gpu * ALGO_OPS[args.cfg],
                       "peak_thread_ops_per_s": issue_peak, "frac": per_gpu * ALGO_OPS[args.cfg] / issue_peak,
-                      "sm_clock_hz": f_clk, "note": "148 SMs x 128 lanes x SM clock during the run"},
+                      "sm_clock_hz": f_clk, "note": "148 SMs x 128 lanes x SM clock during the run",
+                      "measured_peak_imad_thread_ops_per_s": peak_imad, "measured_peak_ffma_thread_ops_per_s": peak_ffma,
+                      "frac_of_measured_imad_peak": per_gpu * ALGO_OPS[args.cfg] / peak_imad if peak_imad > 0 else None},
             "clocks": clk,
             "chi2": chi2_last,
         }

@@ -80,6 +80,7 @@ SIGNATURES = {
     "gsm_comm_destroy": (C.c_int, [_ctx]),
     "gsm_probe": (C.c_int, [_ctx, C.c_int, C.c_int64, C.c_int, C.c_int, _u32p, _u32p, _f32p, _f32p,
                             _f64p, _i32p, _u32p, _f32p, _f64p, _i64p, _i32p]),
+    "gsm_issue_peak": (C.c_int, [_ctx, C.c_int, C.POINTER(C.c_double)]),
 }
 
 _lib = None
@@ -295,6 +296,12 @@ class Mc:
 
     def elapsed_ms(self, sid: int) -> float:
         return float(self.lib.gsm_last_elapsed_ms(self._h, sid))
+
+    def issue_peak(self, kind: int = 0) -> float:
+        """Measured thread-level multiply-adds per second (0: integer, 1: FP32) on this GPU."""
+        v = C.c_double(0.0)
+        self._ck(self.lib.gsm_issue_peak(self._h, kind, C.byref(v)))
+        return float(v.value)
 
     def launch_count(self) -> int:
         return int(self.lib.gsm_launch_count(self._h))

@@ -825,6 +825,40 @@ int gsm_comm_destroy(gsm_ctx* c)
     return GSM_OK;
 }
 
+int gsm_issue_peak(gsm_ctx* c, int kind, double* out)
+{
+    if (!c || !out || (kind != 0 && kind != 1)) return fail(GSM_EINVAL, "bad issue-peak call");
+    CK(cudaSetDevice(c->devid));
+    int sms = 148;
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->devid));
+    unsigned int* d = nullptr;
+    CK(cudaMalloc(&d, sizeof(unsigned int)));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    const int grid = sms * 8, iters = 1 << 15;   // 8 x 256 threads per SM: every scheduler busy
+    double best = 0.0;
+    cudaError_t e = cudaSuccess;
+    for (int rep = 0; rep < 4 && e == cudaSuccess; ++rep) {   // first pass warms the clocks up
+        cudaEventRecord(e0, 0);
+        e = launch_issue_probe(d, grid, iters, kind == 0, 0);
+        cudaEventRecord(e1, 0);
+        if (e == cudaSuccess) e = cudaEventSynchronize(e1);
+        float ms = 0.0f;
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, e0, e1);
+        if (e == cudaSuccess && ms > 0.0f) {
+            const double ops = (double)grid * 256.0 * (double)iters * 16.0 / ((double)ms * 1e-3);
+            if (ops > best) best = ops;
+        }
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d);
+    CK(e);
+    *out = best;
+    return GSM_OK;
+}
+
 int gsm_probe(gsm_ctx* c, int what, int64_t n, int ni, int nj, const uint32_t* w0,
               const uint32_t* w1, const float* f0, const float* f1, const double* d0,
               const int32_t* i0, uint32_t* ou, float* of, double* od, int64_t* ol, int32_t* oi)

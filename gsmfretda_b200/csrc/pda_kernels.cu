@@ -244,6 +244,45 @@ cudaError_t launch_u64_to_f32(const unsigned long long* in, float* out, int n, c
     return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------------------------
+// issue-rate probe: the denominator of the instruction-issue roofline.
+// Every thread runs `iters` trips of 16 independent 32-bit multiply-adds (integer variant) or
+// fused multiply-adds (FP32 variant); nothing else is in the loop but its counter.  The host
+// times it with CUDA events: thread-instructions / second, measured on the same clocks as the
+// evaluation kernel.
+// ------------------------------------------------------------------------------------
+template <bool kInt>
+__global__ void __launch_bounds__(256) pda_issue_probe_kernel(unsigned int* out, int iters, unsigned int seed)
+{
+    unsigned int x[16];
+    float f[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        x[k] = seed + threadIdx.x * 16u + (unsigned)k;
+        f[k] = (float)(x[k] & 1023u) * 1e-3f;
+    }
+    const unsigned int m = seed | 1u;
+    const float fm = 1.0f + (float)(seed & 7u) * 1e-7f;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            if (kInt) x[k] = x[k] * m + 12345u;
+            else f[k] = fmaf(f[k], fm, 1e-9f);
+        }
+    }
+    unsigned int acc = 0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) acc ^= kInt ? x[k] : __float_as_uint(f[k]);
+    if (acc == 0xdeadbeefu) out[0] = acc;   // keeps the chains alive
+}
+
+cudaError_t launch_issue_probe(unsigned int* out, int grid, int iters, bool integer, cudaStream_t s)
+{
+    if (integer) pda_issue_probe_kernel<true><<<grid, 256, 0, s>>>(out, iters, 12345u);
+    else pda_issue_probe_kernel<false><<<grid, 256, 0, s>>>(out, iters, 12345u);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_probe(const ProbeArgs& a, cudaStream_t s)
 {
     if (a.n == 0) return cudaSuccess;

@@ -108,5 +108,7 @@ struct ProbeArgs {
     uint32_t* ou; float* of; double* od; long long* ol; int32_t* oi;
 };
 cudaError_t launch_probe(const ProbeArgs& a, cudaStream_t s);
+// 16 independent multiply-adds per trip per thread, 256 threads per block (issue-rate roofline)
+cudaError_t launch_issue_probe(unsigned int* out, int grid, int iters, bool integer, cudaStream_t s);
 
 }  // namespace pda

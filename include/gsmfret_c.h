@@ -170,6 +170,12 @@ int gsm_probe(gsm_ctx* ctx, int what, int64_t n, int ni, int nj, const uint32_t*
               const uint32_t* w1, const float* f0, const float* f1, const double* d0,
               const int32_t* i0, uint32_t* ou, float* of, double* od, int64_t* ol, int32_t* oi);
 
+/* Measured instruction-issue peak of this GPU at its current clocks: thread-level 32-bit
+ * multiply-adds (kind 0: integer IMAD, kind 1: FP32 FFMA) per second over a grid that fills every
+ * SM, timed with CUDA events.  The denominator of the issue roofline bench.py reports
+ * ("INT32-only peak is to be measured by an IMAD micro-benchmark"). */
+int gsm_issue_peak(gsm_ctx* ctx, int kind, double* thread_ops_per_s);
+
 #ifdef __cplusplus
 }
 #endif
