@@ -7,7 +7,9 @@ burst-samples/s) on N B200s of one node.
 A "step" is one evaluation of one parameter vector over the whole synthetic burst set
 (config 2: 1e5 bursts x 100 repeats = 1e7 burst-samples per GPU).  At N > 1 (torchrun) every
 rank holds its own 1e5-burst shard of one N x 1e5-burst dataset (weak scaling) and each step
-all-reduces the histogram with NCCL before chi-square (burst-split mode).
+all-reduces the histogram before chi-square (burst-split mode): by default inside
+the evaluation kernel (its last block stores into every rank's inbox over NVLink,
+--collective peer), or with ncclAllReduce + a finalize launch (--collective nccl).
 --cfg 4 is the GA population: a step is one batch of 1024 parameter vectors over 1e5 bursts x 16
 repeats in ONE launch (gsm_run_batch); at N > 1 the population is split across the ranks with no
 collective (population mode) and the burst data is replicated (strong scaling of the batch).
@@ -200,6 +202,9 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--mode", default="replay", choices=["replay", "normal"],
                     help="replay: bit-exact draw contract (FP64 binomial); normal: FP32 fast arithmetic")
+    ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
+                    help="burst-split histogram reduction at N > 1: peer = fused into the evaluation kernel "
+                         "(stores into every rank's inbox over NVLink), nccl = ncclAllReduce + a finalize launch")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -219,6 +224,7 @@ def main():
     torch.cuda.set_device(local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries the JSON line only
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():
@@ -246,11 +252,17 @@ def main():
     mc.set_mode(capi.GSM_MODE_NORMAL if args.mode == "normal" else capi.GSM_MODE_REPLAY)
     mc.init_bursts(b, g_offset=0 if population else rank * B)
     if world > 1 and not population:
-        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            idt.copy_(torch.frombuffer(bytearray(capi.comm_unique_id()), dtype=torch.uint8))
-        dist.broadcast(idt, 0)
-        mc.comm_init(bytes(idt.cpu().numpy().tobytes()), rank, world)
+        if args.collective == "nccl":
+            idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+            if rank == 0:
+                idt.copy_(torch.frombuffer(bytearray(capi.comm_unique_id()), dtype=torch.uint8))
+            dist.broadcast(idt, 0)
+            mc.comm_init(bytes(idt.cpu().numpy().tobytes()), rank, world)
+        else:
+            mine = torch.frombuffer(bytearray(mc.peer_export(world, 1)), dtype=torch.uint8).cuda()
+            allh = [torch.empty_like(mine) for _ in range(world)]
+            dist.all_gather(allh, mine)
+            mc.peer_connect(b"".join(bytes(h.cpu().numpy().tobytes()) for h in allh), rank, world)
         oh = torch.from_numpy(mc.observed_hist()).cuda()
         dist.all_reduce(oh)  # counts < 2^24: exact in f32
         mc.set_observed_hist(oh.cpu().numpy())
@@ -355,7 +367,9 @@ def main():
                        "repeats": R, "states": n, "param_vectors": P_job, "hist_bins": NB,
                        "sharding": "single GPU" if world == 1 else
                                    (f"population split x{world}, no collective" if population else
-                                    f"burst-split x{world}, NCCL all-reduce of the histogram"),
+                                    (f"burst-split x{world}, histogram all-reduce fused into the evaluation kernel "
+                                     f"(peer stores over NVLink, one launch per step)" if args.collective == "peer" else
+                                     f"burst-split x{world}, NCCL all-reduce of the histogram + finalize launch")),
                        "l2": "256 MiB buffer written between timed iterations (L2 flush)",
                        "timing": "CUDA events on the launching stream per step, summed; max over ranks",
                        "photon_layout": "packed 4 B/photon" if mc.is_packed() else "raw 16 B/photon"},

@@ -20,6 +20,9 @@ GSM_FORCE_RAW64 = 4
 GSM_NO_INDEX = 8
 GSM_MODE_REPLAY = 0
 GSM_MODE_NORMAL = 1
+PEER_HANDLE_BYTES = 128
+GSM_FLAG_STEP_CAP = 1
+GSM_FLAG_PEER_TIMEOUT = 2
 
 _f32p = C.POINTER(C.c_float)
 _f64p = C.POINTER(C.c_double)
@@ -78,6 +81,10 @@ SIGNATURES = {
     "gsm_comm_unique_id": (C.c_int, [C.c_void_p]),
     "gsm_comm_init": (C.c_int, [_ctx, C.c_void_p, C.c_int, C.c_int]),
     "gsm_comm_destroy": (C.c_int, [_ctx]),
+    "gsm_peer_export": (C.c_int, [_ctx, C.c_int, C.c_int, C.c_void_p]),
+    "gsm_peer_connect": (C.c_int, [_ctx, C.c_void_p, C.c_int, C.c_int]),
+    "gsm_peer_disconnect": (C.c_int, [_ctx]),
+    "gsm_peer_set_timeout": (C.c_int, [_ctx, C.c_uint32]),
     "gsm_probe": (C.c_int, [_ctx, C.c_int, C.c_int64, C.c_int, C.c_int, _u32p, _u32p, _f32p, _f32p,
                             _f64p, _i32p, _u32p, _f32p, _f64p, _i64p, _i32p]),
     "gsm_issue_peak": (C.c_int, [_ctx, C.c_int, C.POINTER(C.c_double)]),
@@ -327,6 +334,25 @@ class Mc:
 
     def comm_destroy(self):
         self._ck(self.lib.gsm_comm_destroy(self._h))
+
+    def peer_export(self, world: int, max_P: int = 1) -> bytes:
+        """Allocate this rank's symmetric exchange block; returns the 128-byte handle to gather."""
+        buf = C.create_string_buffer(PEER_HANDLE_BYTES)
+        self._ck(self.lib.gsm_peer_export(self._h, world, max_P, buf))
+        return buf.raw
+
+    def peer_connect(self, handles, rank: int, world: int):
+        """handles: the world handles in rank order (bytes of world x 128, or a list of bytes)."""
+        blob = handles if isinstance(handles, (bytes, bytearray)) else b"".join(handles)
+        assert len(blob) == world * PEER_HANDLE_BYTES, (len(blob), world)
+        buf = C.create_string_buffer(bytes(blob), len(blob))
+        self._ck(self.lib.gsm_peer_connect(self._h, buf, rank, world))
+
+    def peer_disconnect(self):
+        self._ck(self.lib.gsm_peer_disconnect(self._h))
+
+    def peer_set_timeout(self, ms: int):
+        self._ck(self.lib.gsm_peer_set_timeout(self._h, ms))
 
     def evaluate(self, n: int, args, sid: int = 0, N: int | None = None, epoch: int | None = None):
         """The six calls gpuWorker makes per evaluation (gpuWorker.cpp:71-80), then wait.

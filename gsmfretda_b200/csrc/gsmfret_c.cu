@@ -5,6 +5,7 @@
 #include "pda_kernels.h"
 
 #include <dlfcn.h>
+#include <unistd.h>
 #include <atomic>
 #include <cmath>
 #include <cstdarg>
@@ -103,6 +104,7 @@ struct Slot {
     long long* d_cnt = nullptr; long long* h_cnt = nullptr;
     int32_t* d_steps = nullptr; int32_t* h_steps = nullptr;
     bool ran = false;
+    uint32_t peer_seq = 0;   // evaluations exchanged on this slot so far
 };
 
 struct gsm_ctx {
@@ -133,7 +135,43 @@ struct gsm_ctx {
     std::atomic<uint64_t> launches{0};
     void* comm = nullptr;
     int rank = 0, world = 1;
+    // fused peer exchange (gsm_peer_export / gsm_peer_connect)
+    unsigned long long* peer_base = nullptr;   // this rank's symmetric block, all slots
+    size_t peer_bytes = 0;
+    size_t peer_slot_words = 0;                // u64 words per slot
+    int peer_cap_P = 0, peer_nbp = 0, peer_world = 0;
+    bool peer_on = false;
+    unsigned long long* peer_map[kMaxPeers] = {nullptr};
+    bool peer_ipc[kMaxPeers] = {false};
+    uint32_t peer_timeout_ms = 20000;
 };
+
+// what travels between ranks to map each other's symmetric block
+struct PeerHandle {
+    uint32_t magic;
+    uint32_t pid;
+    int32_t devid;
+    int32_t world;
+    uint64_t ptr;
+    uint64_t bytes;
+    cudaIpcMemHandle_t ipc;   // 64 bytes
+    unsigned char pad[128 - 32 - sizeof(cudaIpcMemHandle_t)];
+};
+static_assert(sizeof(PeerHandle) == GSM_PEER_HANDLE_BYTES, "peer handle is 128 bytes");
+constexpr uint32_t kPeerMagic = 0x47534d50u;  // "GSMP"
+static void peer_release(gsm_ctx* c)
+{
+    for (int r = 0; r < kMaxPeers; ++r) {
+        if (c->peer_ipc[r] && c->peer_map[r]) cudaIpcCloseMemHandle(c->peer_map[r]);
+        c->peer_map[r] = nullptr;
+        c->peer_ipc[r] = false;
+    }
+    if (c->peer_base) cudaFree(c->peer_base);
+    c->peer_base = nullptr;
+    c->peer_bytes = 0; c->peer_on = false; c->peer_world = 0; c->peer_cap_P = 0;
+    cudaGetLastError();
+}
+
 
 static inline size_t res_bytes(int P, int nbp)
 {
@@ -337,8 +375,10 @@ void gsm_destroy(gsm_ctx* c)
     if (!c) return;
     cudaSetDevice(c->devid);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
-    for (Slot& s : c->slots) {
+    for (Slot& s : c->slots)
         if (s.stream) cudaStreamSynchronize(s.stream);
+    peer_release(c);
+    for (Slot& s : c->slots) {
         cudaFreeHost(s.h_params); cudaFree(s.d_params);
         cudaFree(s.d_whist); cudaFree(s.d_counters); cudaFree(s.d_res); cudaFreeHost(s.h_res);
         cudaFree(s.d_mcE); cudaFreeHost(s.h_mcE);
@@ -653,7 +693,17 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
     a.n_steps = (c->flags & GSM_KEEP_COUNTS) ? s.d_steps : nullptr;
     a.b0 = 0; a.N = N; a.g_offset = c->g_offset;
     a.R = c->R; a.P = s.P; a.nb = c->nb; a.left_pad = c->left_pad;
-    a.finalize = c->comm ? 0 : 1;
+    a.finalize = c->comm ? 0 : (c->peer_on ? 2 : 1);
+    if (c->peer_on) {
+        if (s.P > c->peer_cap_P) return fail(GSM_EINVAL, "%d vectors exceed the peer exchange capacity %d", s.P, c->peer_cap_P);
+        if (nbp != c->peer_nbp) return fail(GSM_ESTATE, "histogram size changed after gsm_peer_export");
+        for (int rk = 0; rk < c->peer_world; ++rk) a.peer.block[rk] = c->peer_map[rk] + (size_t)sid * c->peer_slot_words;
+        a.peer.stride = (unsigned long long)c->peer_cap_P * nbp;
+        a.peer.seq = ++s.peer_seq;
+        a.peer.world = c->peer_world;
+        a.peer.rank = c->rank;
+        a.peer.timeout_ms = c->peer_timeout_ms;
+    }
     a.seed = c->seed; a.epoch0 = s.epoch;
     a.clk_p = c->clk_p; a.bg_ad_rate = c->bg_ad; a.bg_dd_rate = c->bg_dd;
 
@@ -797,6 +847,7 @@ int gsm_comm_unique_id(void* out128)
 int gsm_comm_init(gsm_ctx* c, const void* id128, int rank, int world)
 {
     if (!c || !id128 || world < 1 || rank < 0 || rank >= world) return fail(GSM_EINVAL, "rank %d of %d", rank, world);
+    if (c->peer_on) return fail(GSM_ESTATE, "the peer exchange is connected: use one reduction or the other");
     int r = nccl_load();
     if (r) return r;
     CK(cudaSetDevice(c->devid));
@@ -822,6 +873,84 @@ int gsm_comm_destroy(gsm_ctx* c)
         c->comm = nullptr;
     }
     c->rank = 0; c->world = 1;
+    return GSM_OK;
+}
+
+int gsm_peer_export(gsm_ctx* c, int world, int max_P, void* handle_out)
+{
+    if (!c || !handle_out || world < 1 || world > kMaxPeers || max_P < 1)
+        return fail(GSM_EINVAL, "peer export: world %d (1..%d), max_P %d", world, kMaxPeers, max_P);
+    if (c->comm) return fail(GSM_ESTATE, "an NCCL communicator is attached: use one reduction or the other");
+    CK(cudaSetDevice(c->devid));
+    for (Slot& s : c->slots) CK(cudaStreamSynchronize(s.stream));
+    peer_release(c);
+    const int nbp = c->nb + 2;
+    c->peer_slot_words = kPeerFlagWords + (size_t)2 * world * max_P * nbp;
+    c->peer_bytes = c->slots.size() * c->peer_slot_words * sizeof(unsigned long long);
+    CK(cudaMalloc((void**)&c->peer_base, c->peer_bytes));
+    CK(cudaMemset(c->peer_base, 0, c->peer_bytes));
+    c->peer_cap_P = max_P; c->peer_nbp = nbp; c->peer_world = world;
+    for (Slot& s : c->slots) s.peer_seq = 0;
+    PeerHandle h;
+    memset(&h, 0, sizeof(h));
+    h.magic = kPeerMagic; h.pid = (uint32_t)getpid(); h.devid = c->devid; h.world = world;
+    h.ptr = (uint64_t)(uintptr_t)c->peer_base; h.bytes = c->peer_bytes;
+    CK(cudaIpcGetMemHandle(&h.ipc, c->peer_base));
+    memcpy(handle_out, &h, sizeof(h));
+    return GSM_OK;
+}
+
+int gsm_peer_connect(gsm_ctx* c, const void* handles, int rank, int world)
+{
+    if (!c || !handles || world < 1 || world > kMaxPeers || rank < 0 || rank >= world)
+        return fail(GSM_EINVAL, "peer connect: rank %d of %d", rank, world);
+    if (!c->peer_base || c->peer_world != world) return fail(GSM_ESTATE, "gsm_peer_export(world = %d) has not run", world);
+    CK(cudaSetDevice(c->devid));
+    const PeerHandle* hs = (const PeerHandle*)handles;
+    for (int r = 0; r < world; ++r) {
+        PeerHandle h;
+        memcpy(&h, hs + r, sizeof(h));
+        if (h.magic != kPeerMagic || h.world != world || h.bytes != c->peer_bytes)
+            return fail(GSM_EINVAL, "peer handle %d does not match (world %d, %llu bytes)", r, h.world, (unsigned long long)h.bytes);
+        if (r == rank) {
+            if (h.ptr != (uint64_t)(uintptr_t)c->peer_base || h.pid != (uint32_t)getpid())
+                return fail(GSM_EINVAL, "handle %d is not this context's export", r);
+            c->peer_map[r] = c->peer_base;
+        } else if (h.pid == (uint32_t)getpid()) {
+            // another context of this process: the pointer is already valid here
+            if (h.devid != c->devid) {
+                cudaError_t e = cudaDeviceEnablePeerAccess(h.devid, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+                    return fail(GSM_ECUDA, "cudaDeviceEnablePeerAccess(%d) returned %s(%d)", h.devid, cudaGetErrorString(e), (int)e);
+                cudaGetLastError();
+            }
+            c->peer_map[r] = (unsigned long long*)(uintptr_t)h.ptr;
+        } else {
+            void* m = nullptr;
+            CK(cudaIpcOpenMemHandle(&m, h.ipc, cudaIpcMemLazyEnablePeerAccess));
+            c->peer_map[r] = (unsigned long long*)m;
+            c->peer_ipc[r] = true;
+        }
+    }
+    c->rank = rank; c->world = world;
+    c->peer_on = world > 1;
+    return GSM_OK;
+}
+
+int gsm_peer_disconnect(gsm_ctx* c)
+{
+    if (!c) return fail(GSM_EINVAL, "null context");
+    CK(cudaSetDevice(c->devid));
+    for (Slot& s : c->slots) CK(cudaStreamSynchronize(s.stream));
+    peer_release(c);
+    c->rank = 0; c->world = 1;
+    return GSM_OK;
+}
+
+int gsm_peer_set_timeout(gsm_ctx* c, uint32_t ms)
+{
+    if (!c || ms == 0) return fail(GSM_EINVAL, "timeout of %u ms", ms);
+    c->peer_timeout_ms = ms;
     return GSM_OK;
 }
 

@@ -352,6 +352,70 @@ __device__ __forceinline__ void finalize_block(const EvalArgs& a)
     }
 }
 
+// ---- fused cross-GPU reduction (burst-split sharding) ---------------------------------
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v)
+{
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p)
+{
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long* p)
+{
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// One-shot all-reduce of the working histogram by the last block of every rank: push the
+// partial bins into every rank's inbox over NVLink, release an arrival flag, wait for the
+// flags of all senders in the LOCAL block (no polling across the link), sum in rank order.
+// Integer bins: the sum does not depend on arrival order, so every rank holds identical bits.
+__device__ __forceinline__ void peer_exchange_block(const EvalArgs& a)
+{
+    const PeerArgs& pe = a.peer;
+    const int nbp = a.nb + 2;
+    const size_t tot = (size_t)a.P * nbp;
+    const unsigned par = pe.seq & 1u;
+    const size_t my_section = kPeerFlagWords + ((size_t)par * pe.world + pe.rank) * pe.stride;
+    for (int r = 0; r < pe.world; ++r) {
+        unsigned long long* dst = pe.block[r] + my_section;
+        for (size_t i = threadIdx.x; i < tot; i += blockDim.x) dst[i] = __ldcg(a.whist + i);
+    }
+    __threadfence_system();
+    __syncthreads();
+    if ((int)threadIdx.x < pe.world)
+        st_release_sys(pe.block[threadIdx.x] + par * kMaxPeers + pe.rank, (unsigned long long)pe.seq);
+    if ((int)threadIdx.x < pe.world) {
+        const unsigned long long* f = pe.block[pe.rank] + par * kMaxPeers + threadIdx.x;
+        const unsigned long long t0 = global_ns();
+        while (ld_acquire_sys(f) != (unsigned long long)pe.seq) {
+            __nanosleep(200);
+            if (global_ns() - t0 > (unsigned long long)pe.timeout_ms * 1000000ull) {
+                atomicOr(a.counters + 2, 2ull);   // a peer never arrived: results are partial
+                break;
+            }
+        }
+    }
+    __syncthreads();
+    const unsigned long long* in = pe.block[pe.rank] + kPeerFlagWords + (size_t)par * pe.world * pe.stride;
+    for (size_t i = threadIdx.x; i < tot; i += blockDim.x) {
+        unsigned long long s = 0ull;
+        for (int r = 0; r < pe.world; ++r) s += ld_relaxed_sys(in + (size_t)r * pe.stride + i);
+        a.whist[i] = s;
+    }
+    __syncthreads();
+}
+
 // Persistent, warp-autonomous evaluation kernel.
 //   kLayout 0: raw int64 burst_ad/burst_dd (fallback), 1: packed words scanned photon by
 //   photon, 2: packed words + running-max / next-photon index (O(log ph) windows).
@@ -548,6 +612,7 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
     if (s_last) {
         __threadfence();
         if (a.finalize) {
+            if (a.finalize == 2) peer_exchange_block(a);
             finalize_block(a);
         } else if (threadIdx.x == 0) {
             a.counters[0] = 0ull;

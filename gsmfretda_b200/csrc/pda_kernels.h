@@ -7,6 +7,8 @@
 namespace pda {
 
 constexpr int kMaxStates = 8;
+constexpr int kMaxPeers = 8;      // GPUs of one NVSwitch domain that can split one dataset
+constexpr int kPeerFlagWords = 2 * kMaxPeers;  // arrival flags [parity][sender] in front of the inboxes
 
 // One burst, 32 bytes, read with two 16-byte loads (role of the reference's five parallel
 // per-burst arrays start/stop/istart/phCount/T, /root/reference/src/mc.cu:456-521).
@@ -36,6 +38,22 @@ struct ParamRaw {
     float p[8];       // unnormalised inflow rates
 };
 
+// Cross-GPU histogram exchange fused into the evaluation kernel (burst-split sharding,
+// SURVEY.md §8e).  Every rank owns one symmetric block per stream slot,
+//   u64 flag[2][kMaxPeers] | u64 inbox[2][world][stride]
+// mapped into every peer's address space (CUDA IPC over NVLink, or the same pointer inside one
+// process).  The last block of a rank's launch stores its partial histogram into inbox[parity]
+// [rank] of EVERY rank, releases flag[parity][rank] = seq there, then waits on its own flags and
+// sums its own inboxes: a one-shot all-reduce without a second launch or a library call.
+struct PeerArgs {
+    unsigned long long* block[kMaxPeers];  // rank r's block for this slot, in this process' mapping
+    unsigned long long stride;             // u64 words per sender section (capacity P x (nb+2))
+    uint32_t seq;                          // evaluation number on the slot (>= 1); parity selects the buffer
+    int32_t world;
+    int32_t rank;
+    uint32_t timeout_ms;                   // give up waiting for a peer after this long (flag bit 1)
+};
+
 struct EvalArgs {
     const BurstRec* bursts;
     const int32_t* pk;         // packed photons, (rel_tick << 2) | acceptor << 1 | donor ; or null
@@ -62,9 +80,11 @@ struct EvalArgs {
     int32_t nb;
     int32_t left_pad;
     int32_t finalize;          // 1: the last block reduces chi2 and resets the working set
+                               // 2: the same after the peer exchange (PeerArgs); 0: leave whist for a library all-reduce
     uint32_t seed;
     uint32_t epoch0;           // parameter vector p draws with epoch0 + p
     float clk_p, bg_ad_rate, bg_dd_rate;
+    PeerArgs peer;
 };
 
 struct LaunchCfg {

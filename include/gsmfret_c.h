@@ -148,7 +148,8 @@ const float* gsm_result_mcE(const gsm_ctx* ctx, int sid);
 /* per-sample integer acceptor counts / dwell steps (need GSM_KEEP_COUNTS) */
 const int64_t* gsm_result_counts(const gsm_ctx* ctx, int sid);
 const int32_t* gsm_result_steps(const gsm_ctx* ctx, int sid);
-/* bit 0: a sample hit the dwell-step cap (2^20; rates <= 0 hang the reference) */
+/* bit 0: a sample hit the dwell-step cap (2^20; rates <= 0 hang the reference)
+ * bit 1: the peer exchange timed out waiting for another rank (the histogram is partial) */
 uint64_t gsm_result_flags(const gsm_ctx* ctx, int sid);
 /* device time of the last run on the slot between its first and last enqueued operation, ms */
 float gsm_last_elapsed_ms(gsm_ctx* ctx, int sid);
@@ -161,6 +162,25 @@ uint64_t gsm_launch_count(const gsm_ctx* ctx);
 int gsm_comm_unique_id(void* out128);               /* ncclGetUniqueId, 128 bytes */
 int gsm_comm_init(gsm_ctx* ctx, const void* id128, int rank, int world);
 int gsm_comm_destroy(gsm_ctx* ctx);
+
+/* The same reduction fused into the evaluation kernel (no library call, no second launch): the
+ * last block of every rank's launch stores its partial histogram into an inbox on EVERY rank —
+ * peer memory over NVLink / NVSwitch, mapped with CUDA IPC between processes or used directly
+ * between contexts of one process — raises an arrival flag there, waits on its own flags and
+ * sums its own inboxes, then takes chi-square.  Integer bins: every rank ends with identical bits.
+ *   1. every rank: gsm_peer_export(ctx, world, max_P, handle)  (allocates the symmetric block;
+ *      max_P = most parameter vectors per launch; call after gsm_set_hist)
+ *   2. the caller gathers the world handles in rank order (any transport)
+ *   3. every rank: gsm_peer_connect(ctx, handles, rank, world)
+ * Every rank must then issue the same sequence of gsm_run* calls per stream slot.  A rank whose
+ * peer does not arrive within the timeout (default 20 s) reports flag bit 1 in gsm_result_flags.
+ * Exclusive with gsm_comm_init. */
+#define GSM_PEER_HANDLE_BYTES 128
+#define GSM_MAX_PEERS 8
+int gsm_peer_export(gsm_ctx* ctx, int world, int max_P, void* handle_out128);
+int gsm_peer_connect(gsm_ctx* ctx, const void* handles /* world x 128 bytes */, int rank, int world);
+int gsm_peer_disconnect(gsm_ctx* ctx);
+int gsm_peer_set_timeout(gsm_ctx* ctx, uint32_t milliseconds);
 
 /* primitive probes: one element per input through the device code, for the unit tests
  * (role of the reference's test kernels, /root/reference/tests/GenRandTest.cu:107-135,272-287).

@@ -10,6 +10,10 @@ import sys
 
 import pytest
 
+# the peer-exchange tests put up to 8 ranks on ONE device: each rank's stream needs its own
+# hardware queue, or a spinning last block can sit in front of the kernel it is waiting for
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "oracle"))
