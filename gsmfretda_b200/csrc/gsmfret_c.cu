@@ -79,6 +79,8 @@ struct ResultHeader {
     unsigned long long reserved;
 };
 
+constexpr int kDirectResultMaxP = 16;   // up to this many vectors the kernel writes results to host memory itself
+
 struct Slot {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -97,6 +99,7 @@ struct Slot {
     unsigned long long* d_counters = nullptr;
     unsigned char* d_res = nullptr;
     unsigned char* h_res = nullptr;  // pinned mirror: header | hist[P][nbp] | chi2[P]
+    unsigned char* h_res_dev = nullptr;  // the same memory as the device sees it (mapped)
     int res_P = 0, res_nbp = 0;
     // optional per-sample outputs
     size_t cap_samples = 0;
@@ -260,7 +263,8 @@ static int ensure_result_cap(gsm_ctx* c, Slot& s, int P, int64_t N)
         if (s.d_whist) CK(cudaFree(s.d_whist));
         s.d_res = nullptr; s.h_res = nullptr; s.d_whist = nullptr; s.cap_res = 0;
         CK(cudaMalloc((void**)&s.d_res, need));
-        CK(cudaHostAlloc((void**)&s.h_res, need, cudaHostAllocDefault));
+        CK(cudaHostAlloc((void**)&s.h_res, need, cudaHostAllocMapped));
+        CK(cudaHostGetDevicePointer((void**)&s.h_res_dev, s.h_res, 0));
         CK(cudaMalloc((void**)&s.d_whist, need));
         CK(cudaMemsetAsync(s.d_whist, 0, need, s.stream));
         CK(cudaMemsetAsync(s.d_res, 0, need, s.stream));
@@ -684,9 +688,13 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
     a.bursts = c->d_bursts; a.pk = c->d_pk; a.pm = c->d_pm; a.nx = c->d_nx; a.cw = c->d_cw; a.ad = c->d_ad; a.dd = c->d_dd;
     a.params = s.d_params; a.ohist = c->d_ohist;
     a.whist = s.d_whist;
-    a.hist_out = res_hist(s.d_res);
-    a.chi2_out = res_chi2(s.d_res, s.P, nbp);
-    a.flags_out = (unsigned long long*)s.d_res;
+    // few vectors: the last block writes the result block straight into the pinned host mirror
+    // (one launch, no copy on the stream); batches go through device memory and one DMA
+    const bool direct = s.P <= kDirectResultMaxP;
+    unsigned char* res = direct ? s.h_res_dev : s.d_res;
+    a.hist_out = res_hist(res);
+    a.chi2_out = res_chi2(res, s.P, nbp);
+    a.flags_out = (unsigned long long*)res;
     a.counters = s.d_counters;
     a.mcE = (c->flags & GSM_KEEP_MCE) ? s.d_mcE : nullptr;
     a.sum_ai = (c->flags & GSM_KEEP_COUNTS) ? s.d_cnt : nullptr;
@@ -708,7 +716,12 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
     a.clk_p = c->clk_p; a.bg_ad_rate = c->bg_ad; a.bg_dd_rate = c->bg_dd;
 
     CK(cudaEventRecord(s.ev0, s.stream));
-    if (upload) {
+    if (s.P == 1 && !c->comm) {
+        // one vector: it rides in the launch parameters (run_resident re-sends the same bytes)
+        a.use_inl = 1;
+        a.inl = s.h_params[0];
+        s.params_resident = true;
+    } else if (upload) {
         CK(cudaMemcpyAsync(s.d_params, s.h_params, (size_t)s.P * sizeof(ParamRaw), cudaMemcpyHostToDevice, s.stream));
         s.params_resident = true;
     }
@@ -720,7 +733,7 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
         CK(launch_finalize(a, s.stream));
         c->launches += 1;
     }
-    CK(cudaMemcpyAsync(s.h_res, s.d_res, res_bytes(s.P, nbp), cudaMemcpyDeviceToHost, s.stream));
+    if (!direct) CK(cudaMemcpyAsync(s.h_res, s.d_res, res_bytes(s.P, nbp), cudaMemcpyDeviceToHost, s.stream));
     const size_t samples = (size_t)s.P * (size_t)N * (size_t)c->R;
     if (samples) {
         if (a.mcE) CK(cudaMemcpyAsync(s.h_mcE, s.d_mcE, samples * sizeof(float), cudaMemcpyDeviceToHost, s.stream));

@@ -14,7 +14,7 @@
 namespace pda {
 
 constexpr int kBlock = 256;
-constexpr int kChunk = 256;             // consecutive samples a warp draws per ticket
+constexpr int kChunkMax = 256;          // most consecutive samples a warp draws per ticket (EvalArgs::chunk)
 constexpr int kMaxBins = 1024;          // nb + 2 <= kMaxBins
 constexpr uint32_t kStepCap = 1u << 20; // guards the GPU against rates <= 0 (a hang in the reference)
 
@@ -331,13 +331,64 @@ __device__ __forceinline__ float chi2_of(const unsigned long long* __restrict__ 
     return chisqr / (float)(effN - n_states * (n_states + 1));
 }
 
-// chi2 for every p, copy the histogram out, re-zero the working set (whole block)
-__device__ __forceinline__ void finalize_block(const EvalArgs& a)
+// The same number by the whole block, for launches of a few vectors: every thread prepares the
+// term of one bin (the L2 round trips and the FP64 division overlap instead of queueing behind
+// each other: the one-thread loop costs ~50 us for 200 bins, most of a small evaluation), then
+// one thread folds the terms in the host loop's order.  An empty bin contributes +0.0, which
+// leaves the float-rounded running sum unchanged, so the bits equal chi2_of's.
+__device__ __forceinline__ float chi2_block(const unsigned long long* __restrict__ mh,
+                                            const float* __restrict__ oh, int nb, int R,
+                                            int left_pad, int n_states, double* s_term, int* s_empty)
 {
+    const float fR = (float)R;
+    if (threadIdx.x == 0) *s_empty = 0;
+    __syncthreads();
+    int empty = 0;
+    for (int i = left_pad + (int)threadIdx.x; i < nb; i += blockDim.x) {
+        const float M = __ull2float_rn(__ldcg(mh + i));
+        double term = 0.0;
+        if (M > 0.0f) {
+            const float mr = M / fR;
+            const float d = oh[i] - mr;
+            const double num = (double)d * (double)d;
+            term = num / (double)mr;
+        } else {
+            empty++;
+        }
+        s_term[i] = term;
+    }
+    if (empty) atomicAdd(s_empty, empty);
+    __syncthreads();
+    float chisqr = 0.0f;
+    if (threadIdx.x == 0) {
+#pragma unroll 8
+        for (int i = left_pad; i < nb; ++i) chisqr = (float)((double)chisqr + s_term[i]);
+        const int effN = nb - left_pad - *s_empty;
+        chisqr = chisqr / (float)(effN - n_states * (n_states + 1));
+    }
+    __syncthreads();
+    return chisqr;   // valid in thread 0
+}
+
+constexpr int kChi2BlockMaxP = 16;   // beyond this one thread per vector is faster than one block per vector
+
+// chi2 for every p, copy the histogram out, re-zero the working set (whole block).
+// s_term: nb doubles of shared memory.
+__device__ __forceinline__ void finalize_block(const EvalArgs& a, double* s_term)
+{
+    __shared__ int s_empty;
     const int nbp = a.nb + 2;
-    for (int p = threadIdx.x; p < a.P; p += blockDim.x)
-        a.chi2_out[p] = chi2_of(a.whist + (size_t)p * nbp, a.ohist, a.nb, a.R, a.left_pad,
-                                a.params[p].n);
+    if (a.P <= kChi2BlockMaxP) {
+        for (int p = 0; p < a.P; ++p) {
+            const float c = chi2_block(a.whist + (size_t)p * nbp, a.ohist, a.nb, a.R, a.left_pad,
+                                       a.use_inl ? a.inl.n : a.params[p].n, s_term, &s_empty);
+            if (threadIdx.x == 0) a.chi2_out[p] = c;
+        }
+    } else {
+        for (int p = threadIdx.x; p < a.P; p += blockDim.x)
+            a.chi2_out[p] = chi2_of(a.whist + (size_t)p * nbp, a.ohist, a.nb, a.R, a.left_pad,
+                                    a.params[p].n);
+    }
     __syncthreads();
     const size_t tot = (size_t)a.P * nbp;
     for (size_t i = threadIdx.x; i < tot; i += blockDim.x) {
@@ -420,17 +471,17 @@ __device__ __forceinline__ void peer_exchange_block(const EvalArgs& a)
 //   kLayout 0: raw int64 burst_ad/burst_dd (fallback), 1: packed words scanned photon by
 //   photon, 2: packed words + running-max / next-photon index (O(log ph) windows).
 // Every warp owns a copy of the parameter vector and a private histogram in shared memory,
-// draws chunks of kChunk consecutive samples from one global ticket, and only meets the other
+// draws chunks of a.chunk consecutive samples from one global ticket, and only meets the other
 // warps of its block once, at the very end (last-block finalisation).
 #ifndef PDA_MIN_BLOCKS
 #define PDA_MIN_BLOCKS 4
 #endif
 template <int kLayout, bool kBg, bool kFast>
-__global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const EvalArgs a)
+__global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const __grid_constant__ EvalArgs a)
 {
     constexpr int kWarps = kBlock / 32;
     __shared__ SmemParams s_params[kWarps];
-    extern __shared__ unsigned int s_hist_all[];  // [kWarps][nbp]
+    extern __shared__ __align__(16) unsigned int s_hist_all[];  // [kWarps][nbp]; the last block reuses it for chi2 terms
     __shared__ int s_last;
     __shared__ WarpCtl s_ctl[kWarps];
 
@@ -442,7 +493,7 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
     unsigned int* hist = s_hist_all + wid * nbp;
 
     const int64_t per_p = a.N * (int64_t)a.R;  // samples per parameter vector
-    const unsigned long long chunks_per_p = (unsigned long long)((per_p + kChunk - 1) / kChunk);
+    const unsigned long long chunks_per_p = (unsigned long long)((per_p + a.chunk - 1) >> a.chunk_log2);
     const unsigned long long items = chunks_per_p * (unsigned long long)a.P;
     const bool small = per_p < (1ll << 31) && items < (1ull << 32);
 
@@ -507,18 +558,18 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
                         }
                     }
                     __syncwarp();
-                    stage_params(sp, a.params + p, lane);
+                    stage_params(sp, a.use_inl ? &a.inl : a.params + p, lane);
                     if (lane == 0) { wc.cur_p = p; wc.epoch = a.epoch0 + (uint32_t)p; }
                     __syncwarp();
                 }
                 const unsigned long long c = item - (unsigned long long)p * chunks_per_p;
-                const int64_t t0 = (int64_t)c * kChunk;
+                const int64_t t0 = (int64_t)(c << a.chunk_log2);
                 const int64_t left = per_p - t0;
                 const int64_t bl0 = small ? (int64_t)((uint32_t)t0 / (uint32_t)a.R) : t0 / a.R;
                 __syncwarp();
                 if (lane == 0) {
                     wc.have_pending = 0;
-                    wc.c_cnt = left < kChunk ? (int)left : kChunk;
+                    wc.c_cnt = left < a.chunk ? (int)left : a.chunk;
                     wc.c_bl = (uint32_t)bl0;
                     wc.c_rep = (uint32_t)(t0 - bl0 * a.R);
                 }
@@ -613,7 +664,7 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
         __threadfence();
         if (a.finalize) {
             if (a.finalize == 2) peer_exchange_block(a);
-            finalize_block(a);
+            finalize_block(a, reinterpret_cast<double*>(s_hist_all));   // every warp has flushed its bins
         } else if (threadIdx.x == 0) {
             a.counters[0] = 0ull;
             a.counters[1] = 0ull;
@@ -647,10 +698,33 @@ static LaunchCfg eval_launch_cfg_t(int device, int layout, bool with_bg, int nb)
     return LaunchCfg{sms * per, kBlock};
 }
 
-template <bool kFast>
-static cudaError_t launch_eval_t(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s)
+// Chunk and grid for one launch.  Large jobs: 256-sample chunks (lanes of a warp stay on the same
+// few bursts) on the full persistent grid.  Small jobs (the reference's own scale: a few thousand
+// bursts x 4 repeats) are latency-bound: hand out chunks as small as one sample per lane so that
+// every warp of the machine gets work, and do not launch blocks that would find the queue empty.
+static inline void shape_launch(EvalArgs& a, LaunchCfg& cfg)
 {
-    if (a.nb + 2 > kMaxBins) return cudaErrorInvalidValue;
+    const long long per_p = (long long)a.N * a.R;
+    const long long total = per_p * a.P;
+    const long long warps = (long long)cfg.grid * (kBlock / 32);
+    long long chunk = total / (warps * 4);
+    int lg = 5;                                   // 32, 64, 128 or 256 samples
+    while ((2ll << lg) <= chunk && (2 << lg) <= kChunkMax) ++lg;
+    chunk = 1ll << lg;
+    a.chunk = (int)chunk;
+    a.chunk_log2 = lg;
+    const long long items = ((per_p + chunk - 1) / chunk) * a.P;
+    long long blocks = (items + kBlock / 32 - 1) / (kBlock / 32);
+    if (blocks < 1) blocks = 1;
+    if (blocks < cfg.grid) cfg.grid = (int)blocks;
+}
+
+template <bool kFast>
+static cudaError_t launch_eval_t(const EvalArgs& a_in, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s)
+{
+    if (a_in.nb + 2 > kMaxBins) return cudaErrorInvalidValue;
+    EvalArgs a = a_in;
+    shape_launch(a, cfg);
     const size_t dyn = eval_dyn_smem(a.nb);
 #define PDA_LAUNCH(LAY, BG) pda_eval_kernel<LAY, BG, kFast><<<cfg.grid, cfg.block, dyn, s>>>(a)
     if (layout == 0) { if (with_bg) PDA_LAUNCH(0, true); else PDA_LAUNCH(0, false); }

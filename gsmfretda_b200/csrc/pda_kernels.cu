@@ -22,7 +22,11 @@
 namespace pda {
 
 
-__global__ void __launch_bounds__(kBlock) pda_finalize_kernel(const EvalArgs a) { finalize_block(a); }
+__global__ void __launch_bounds__(kBlock) pda_finalize_kernel(const __grid_constant__ EvalArgs a)
+{
+    extern __shared__ __align__(16) unsigned char s_raw[];   // nb doubles
+    finalize_block(a, reinterpret_cast<double*>(s_raw));
+}
 
 // ------------------------------------------------------------------------------------
 // one-time data preparation: burst records + packed photon words (role of the uploads in
@@ -215,7 +219,7 @@ cudaError_t launch_eval(const EvalArgs& a, int layout, bool with_bg, LaunchCfg c
 
 cudaError_t launch_finalize(const EvalArgs& a, cudaStream_t s)
 {
-    pda_finalize_kernel<<<1, kBlock, 0, s>>>(a);
+    pda_finalize_kernel<<<1, kBlock, (size_t)(a.nb + 2) * sizeof(double), s>>>(a);
     return cudaGetLastError();
 }
 

@@ -79,13 +79,19 @@ struct EvalArgs {
     int32_t P;
     int32_t nb;
     int32_t left_pad;
+    int32_t chunk;             // consecutive samples per ticket (32 << k; set by the launcher)
+    int32_t chunk_log2;
     int32_t finalize;          // 1: the last block reduces chi2 and resets the working set
                                // 2: the same after the peer exchange (PeerArgs); 0: leave whist for a library all-reduce
     uint32_t seed;
     uint32_t epoch0;           // parameter vector p draws with epoch0 + p
     float clk_p, bg_ad_rate, bg_dd_rate;
     PeerArgs peer;
+    // single-vector launches carry the vector in the launch parameters: no upload on the stream
+    int32_t use_inl;
+    ParamRaw inl;
 };
+static_assert(sizeof(EvalArgs) <= 4096, "EvalArgs travels as a kernel parameter");
 
 struct LaunchCfg {
     int grid;
