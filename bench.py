@@ -54,6 +54,16 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)", 1965.0
 
 
+def ncu_traffic(workload: str, mode: str):
+    """DRAM bytes per launch of the evaluation kernel from the committed ncu capture, or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            e = json.load(f).get(f"{workload}/{mode}")
+        return (float(e["bytes"]), e["source"]) if e else (None, None)
+    except Exception:
+        return None, None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
 
@@ -352,6 +362,7 @@ def main():
         value = samples_job * args.steps / (dev_ms * 1e-3)
         algo_bytes = b.algorithmic_bytes() + (612 * P_local if population else 0)
         achieved = algo_bytes / (ms_per_step * 1e-3) / 1e9
+        traffic, traffic_src = ncu_traffic(w.name, args.mode) if (args.bursts is None and args.repeats is None) else (None, None)
         f_clk = (clk.get("sm_mhz") or sm_max) * 1e6
         issue_peak = 148 * 128 * f_clk
         per_gpu = value / world
@@ -385,7 +396,8 @@ def main():
                             "Mc.set_nstates/set_params/setBurstBd/run_kernel/streamQuery + chi2()/hist()")},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": algo_bytes,
                          "note": "the kernel is instruction-issue bound, not HBM bound: see `issue`"},
             "issue": {"algorithmic_thread_ops_per_sample": ALGO_OPS[args.cfg],
