@@ -131,66 +131,87 @@ class ClockSampler:
                 "samples": len(sm), "window": window, "reasons": sorted(reasons)}
 
 
-def cpu_leg(w, sample_bursts, R, seconds_hint=12.0):
-    """Time the reference's CPU path on a bounded sample -> dict for `cpu_baseline`."""
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import oracle_py
-    O = oracle_py.Oracle()
-    cores = O.num_threads()
-    use_ref = oracle_py.have_ref()
-    Rr = R
-    note = ""
-    if use_ref:
-        Rf = oracle_py.Ref()
-        Rr = 1 << (int(R).bit_length() - 1)  # mc::set_reSampleTimes rounds down to 2^k (mc.cu:316)
-        if Rr != R:
-            note = f"; the reference needs a power-of-two reSampleTimes: {R} -> {Rr}"
-    b = w.bursts(n_bursts=sample_bursts)
-    ohist = O.observed_hist(b, NB)
+class CpuPath:
+    """The reference's CPU path for `cpu_baseline` and the `--impl reference` arm: the checker
+    (oracle/_ref = the reference's own kernel source built for the host, else the C port) over a
+    bounded sample of the workload, with all the host threads OpenMP gives it."""
 
-    def once(nb_):
+    def __init__(self, w, sample_bursts, R):
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import oracle_py
+        self.w = w
+        self.O = oracle_py.Oracle()
+        self.cores = self.O.num_threads()
+        self.use_ref = oracle_py.have_ref()
+        self.R = R
+        self.note = ""
+        if self.use_ref:
+            self.Rf = oracle_py.Ref()
+            self.R = 1 << (int(R).bit_length() - 1)  # mc::set_reSampleTimes rounds down to 2^k (mc.cu:316)
+            if self.R != R:
+                self.note = f"; the reference needs a power-of-two reSampleTimes: {R} -> {self.R}"
+        self.sample_bursts = sample_bursts
+        self.b = w.bursts(n_bursts=sample_bursts)
+        self.ohist = self.O.observed_hist(self.b, NB)
+        probe_n = max(1, min(sample_bursts, 2000))
+        self.once(probe_n)
+        self.rate = probe_n / max(self.once(probe_n), 1e-6)   # bursts per second, for sizing
+
+    def once(self, nb_):
+        w, O = self.w, self.O
         t0 = time.perf_counter()
-        if use_ref:
-            e = Rf.mc_kernel(b, w.n_states, w.args[0], Rr, SEED & 0xFFFFFFFF, 1, N=nb_)
+        if self.use_ref:
+            e = self.Rf.mc_kernel(self.b, w.n_states, w.args[0], self.R, SEED & 0xFFFFFFFF, 1, N=nb_)
             h = O.hist(e, NB)                     # streamWorker's host histogram + chi-square
-            O.chi2(ohist, h, NB, Rr, LEFT_PAD, w.n_states)
+            O.chi2(self.ohist, h, NB, self.R, LEFT_PAD, w.n_states)
         else:
-            O.eval_chi2(b, w.n_states, w.args[0], Rr, SEED & 0xFFFFFFFF, 1, ohist, NB, LEFT_PAD, 0, nb_)
+            O.eval_chi2(self.b, w.n_states, w.args[0], self.R, SEED & 0xFFFFFFFF, 1, self.ohist, NB, LEFT_PAD, 0, nb_)
         return time.perf_counter() - t0
 
-    probe_n = max(1, min(sample_bursts, 2000))
-    once(probe_n)
-    dt = once(probe_n)
-    nb_ = int(max(probe_n, min(sample_bursts, probe_n * seconds_hint / max(dt, 1e-6))))
-    dt1 = once(nb_)
-    reps = int(max(1, min(64, round(seconds_hint / max(dt1, 1e-6)))))  # whole evaluations, back to back
-    dt = dt1 if reps == 1 else sum(once(nb_) for _ in range(reps))
-    samples = nb_ * Rr * reps
-    return {"value": samples / dt, "unit": "burst-samples/s", "cores": cores,
-            "kind": "reference" if use_ref else "port",
-            "sample": f"{reps} evaluation(s) of {nb_} bursts x {Rr} repeats of {w.name} ({samples} burst-samples, {dt:.2f} s, "
-                      f"{'reference mc_kernel source built for the host (oracle/_ref)' if use_ref else 'C port (oracle/pda_oracle.c)'}"
-                      f" + host histogram + chi-square, OpenMP over samples{note})",
-            "_samples": samples, "_seconds": dt}
+    def timed(self, seconds_hint):
+        """About `seconds_hint` seconds of work -> (burst-samples, seconds, evaluations, bursts each)."""
+        nb_ = int(max(1, min(self.sample_bursts, self.rate * seconds_hint)))
+        dt1 = self.once(nb_)
+        reps = int(max(1, min(64, round(seconds_hint / max(dt1, 1e-6)))))  # whole evaluations, back to back
+        dt = dt1 if reps == 1 else sum(self.once(nb_) for _ in range(reps))
+        return nb_ * self.R * reps, dt, reps, nb_
+
+    def describe(self, samples, dt, reps, nb_):
+        src = ("reference mc_kernel source built for the host (oracle/_ref)" if self.use_ref
+               else "C port (oracle/pda_oracle.c)")
+        return {"unit": "burst-samples/s", "cores": self.cores, "kind": "reference" if self.use_ref else "port",
+                "sample": f"{reps} evaluation(s) of {nb_} bursts x {self.R} repeats of {self.w.name} ({samples} "
+                          f"burst-samples, {dt:.2f} s, {src} + host histogram + chi-square, OpenMP over samples{self.note})"}
+
+
+def cpu_leg(w, sample_bursts, R, seconds_hint=12.0):
+    """Time the reference's CPU path on a bounded sample -> dict for `cpu_baseline`."""
+    cp = CpuPath(w, sample_bursts, R)
+    samples, dt, reps, nb_ = cp.timed(seconds_hint)
+    out = cp.describe(samples, dt, reps, nb_)
+    out["value"] = samples / dt
+    return out
 
 
 def run_reference(args, w, rank):
     if rank != 0:
         return
-    per_step = []
-    leg = None
+    # every step is a bounded sample of the workload, sized so that the whole run stays within
+    # a few minutes whatever K is (about 120 s of CPU work in total)
+    hint = min(5.0, max(0.05, 120.0 / max(1, args.steps + args.warmup)))
+    cp = CpuPath(w, min(w.n_bursts, 100000), w.R)
+    tot_samples, tot_s, last = 0, 0.0, None
     for i in range(args.warmup + args.steps):
-        leg = cpu_leg(w, min(w.n_bursts, 100000), w.R, seconds_hint=5.0 if i >= args.warmup else 1.0)
+        r = cp.timed(hint)
         if i >= args.warmup:
-            per_step.append(leg)
-    tot_samples = sum(l["_samples"] for l in per_step)
-    tot_s = sum(l["_seconds"] for l in per_step)
+            tot_samples += r[0]; tot_s += r[1]; last = r
     val = tot_samples / tot_s
-    cb = {k: v for k, v in leg.items() if not k.startswith("_")}
+    cb = cp.describe(*last)
+    cb["sample"] = f"per step: {cb['sample']}; {args.steps} steps, {tot_samples} burst-samples in {tot_s:.1f} s"
     cb["value"] = val
     out = {"impl": "reference", "metric": "burst-samples/s", "value": val, "unit": "burst-samples/s",
            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-           "ms_per_step": 1e3 * tot_s / max(1, len(per_step)), "higher_is_better": True,
+           "ms_per_step": 1e3 * tot_s / max(1, args.steps), "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "f32 walk + f64 binomial", "data": "synthetic",
            "config": {"workload": w.name, "bursts": w.n_bursts, "repeats": w.R, "states": w.n_states,
                       "param_vectors": 1, "note": "CPU path of the reference on a bounded sample per step"},
@@ -411,7 +432,7 @@ def main():
         }
         if not args.no_cpu:
             cb = cpu_leg(w, min(B, 100000), R, seconds_hint=12.0)
-            out["cpu_baseline"] = {k: v for k, v in cb.items() if not k.startswith("_")}
+            out["cpu_baseline"] = cb
         print(json.dumps(out), flush=True)
     mc.close()
     if world > 1:
