@@ -186,6 +186,13 @@ class mc {
     const uint64_t* hHist(int sid, int p = 0) const { return gsm_result_hist(ctx, sid, p); }
     float hChi2(int sid) const { return gsm_result_chi2(ctx, sid); }
     gsm_ctx* handle() { return ctx; }
+    // burst-split across GPUs, the all-reduce of the histogram fused into the evaluation kernel
+    // (include/gsmfret_c.h: gsm_peer_*).  Every rank: peer_export, gather the handles in rank
+    // order over any transport, peer_connect; init_data_split gives the rank its burst range.
+    void peer_export(int world, int max_P, void* handle128) { GSM_CHECK_RETURN(gsm_peer_export(ctx, world, max_P, handle128)); }
+    void peer_connect(const void* handles, int rank, int world) { GSM_CHECK_RETURN(gsm_peer_connect(ctx, handles, rank, world)); }
+    void peer_disconnect() { GSM_CHECK_RETURN(gsm_peer_disconnect(ctx)); }
+    uint64_t hFlags(int sid) const { return gsm_result_flags(ctx, sid); }
 
   protected:
     gsm_ctx* ctx;
