@@ -117,7 +117,7 @@ static inline double det_exp(double x)
  * Giles' polynomial on w = -log(4p(1-p)). */
 static inline float det_norm_icdf(uint32_t t)
 {
-    float sgn = 1.41421356237309504880f;
+    float sgn = -1.41421356237309504880f;   /* CURAND_SQRT2 is NEGATIVE (curand_globals.h:64): z = -sqrt(2) erfcinv(2p) for t <= 2^31 */
     if (t > 0x80000000u) { t = 0xffffffffu - t; sgn = -sgn; }
     float p = (float)t * 2.3283064365386963e-10f + 1.1641532182693481e-10f;
     float x = 1.0f - 2.0f * p;                 /* in [0, 1) */

@@ -191,6 +191,11 @@ class Ref:
         L.ref_rk_binomial.restype = C.c_long
         L.ref_rk_double.argtypes = [_u32p]; L.ref_rk_double.restype = C.c_double
         L.ref_int_multinomial.argtypes = [_u32p, C.c_int, C.c_int, _f32p, _i32p]
+        _u64p_ = C.POINTER(C.c_uint64)
+        L.ref_mc_kernel_sobol.argtypes = [_i64p, _i64p, _i64p, _i64p, _i64p, _i32p, _f32p, C.c_float,
+                                          C.c_float, C.c_float, _f32p, _f32p, _f32p, _f32p, _f32p,
+                                          C.c_int, C.c_int, C.c_int, _u64p_, _u64p_, C.c_int, _f32p, C.c_int]
+        L.ref_mc_kernel_sobol.restype = None
 
     def params(self, n, args):
         a = np.ascontiguousarray(args, np.float32).copy()
@@ -213,6 +218,51 @@ class Ref:
                                _ptr(Pij, _f32p), _ptr(p, _f32p), N, n, R, seed, epoch, g_offset,
                                _ptr(out, _f32p), nthreads)
         return out
+
+
+    def mc_kernel_sobol(self, b, n, args, R, evals=1, N=None, nthreads=0) -> np.ndarray:
+        """The reference's setup_kernel + mc_kernel with cuRAND's own scrambled Sobol64 sequences
+        (tables from libcurand's host API), `evals` evaluations on persistent RNG states as
+        gpuWorker does -> mcE[evals, N*R]: what the reference's class mc computes on the GPU, up to
+        libdevice-vs-det_math ulps."""
+        assert R & (R - 1) == 0
+        N = b.n_bursts if N is None else N
+        ok, E, v, K, Pij, p = self.params(n, args)
+        assert ok
+        dv, sc = sobol_tables()
+        out = np.zeros((evals, N * R), np.float32)
+        u64p = C.POINTER(C.c_uint64)
+        self.lib.ref_mc_kernel_sobol(_ptr(b.start, _i64p), _ptr(b.stop, _i64p), _ptr(b.burst_ad, _i64p),
+                                     _ptr(b.burst_dd, _i64p), _ptr(b.istart, _i64p), _ptr(b.ph_count, _i32p),
+                                     _ptr(b.T, _f32p), float(b.clk_p), float(b.bg_ad_rate),
+                                     float(b.bg_dd_rate), _ptr(E, _f32p), _ptr(v, _f32p), _ptr(K, _f32p),
+                                     _ptr(Pij, _f32p), _ptr(p, _f32p), N, n, R,
+                                     dv.ctypes.data_as(u64p), sc.ctypes.data_as(u64p), evals,
+                                     out.ctypes.data_as(_f32p), nthreads)
+        return out
+
+
+_SOBOL = None
+
+
+def sobol_tables():
+    """(direction vectors [20000, 64], scramble constants [20000]) of
+    CURAND_SCRAMBLED_DIRECTION_VECTORS_64_JOEKUO6 from libcurand's host API — the tables
+    mc::mc fetches (/root/reference/src/mc.cu:312-314).  Needs no GPU."""
+    global _SOBOL
+    if _SOBOL is None:
+        import glob
+        cands = (glob.glob("/usr/local/cuda/lib64/libcurand.so*") +
+                 glob.glob(os.path.join(os.path.dirname(np.__file__), "..", "nvidia", "curand", "lib", "libcurand.so*")))
+        if not cands:
+            raise FileNotFoundError("libcurand.so")
+        lib = C.CDLL(cands[0])
+        p = C.POINTER(C.c_uint64)()
+        q = C.POINTER(C.c_uint64)()
+        assert lib.curandGetDirectionVectors64(C.byref(p), 104) == 0   # CURAND_SCRAMBLED_DIRECTION_VECTORS_64_JOEKUO6
+        assert lib.curandGetScrambleConstants64(C.byref(q)) == 0
+        _SOBOL = (np.ctypeslib.as_array(p, shape=(20000, 64)).copy(), np.ctypeslib.as_array(q, shape=(20000,)).copy())
+    return _SOBOL
 
 
 def have_ref() -> bool:

@@ -45,21 +45,51 @@ struct curandStateScrambledSobol64 {
     int phase;    /* 0 before the initial-state draw, 1 next-state, 2 dwell, 3 inside window */
     int bg_calls; /* Poisson draws made in this step */
     int seeded;   /* curand() for rk_seed already served */
+    /* second personality (ref_mc_kernel_sobol): cuRAND's own scrambled Sobol64 generator,
+     * restated from the toolkit's curand_kernel.h (state i/x/c + 64 direction vectors, gray-code
+     * update, skipahead), so the reference code draws what it draws on the GPU */
+    int sobol;
+    unsigned long long i, x, c;
+    const unsigned long long *dv;
 };
+
+static inline unsigned long long sobol_next(curandStateScrambledSobol64 *s)
+{
+    /* curand(curandStateScrambledSobol64_t*), curand_kernel.h:1582-1591 */
+    unsigned long long res = s->x;
+    s->x ^= s->dv[__builtin_ctzll(~s->i)];   /* ~i == 0 cannot happen below 2^64 draws */
+    s->i++;
+    return res;
+}
 
 static inline float shim_u01(uint32_t w)
 {
     return (float)w * 2.3283064365386963e-10f + 1.1641532182693481e-10f;
 }
 
-static void curand_init(unsigned long long *, unsigned long long, unsigned long long,
-                        curandStateScrambledSobol64 *)
+static void curand_init(unsigned long long *dirvec, unsigned long long scramble, unsigned long long offset,
+                        curandStateScrambledSobol64 *s)
 {
-    /* direction vectors are not used: the state was pre-loaded with (g, rep, seed, epoch) */
+    /* contract personality: direction vectors are not used, the state was pre-loaded with
+     * (g, rep, seed, epoch) */
+    if (!s->sobol) return;
+    /* curand_init(curandDirectionVectors64_t, scramble_c, offset, state) + skipahead,
+     * curand_kernel.h:1491-1503,1340-1357 */
+    s->dv = dirvec;
+    s->c = scramble;
+    s->i = offset;
+    s->x = s->c;
+    const unsigned long long gray = s->i ^ (s->i >> 1);
+    for (unsigned k = 0; k < 64; k++)
+        if (gray & (1ULL << k)) s->x ^= s->dv[k];
 }
+
+/* _curand_poisson_ITR_double (curand_poisson.h:436-462) on a 64-bit word */
+static unsigned int shim_poisson_itr(uint64_t x, double lambda);
 
 static unsigned long long curand(curandStateScrambledSobol64 *s)
 {
+    if (s->sobol) return sobol_next(s);
     if (s->seeded) { fprintf(stderr, "ref_shim: unexpected curand()\n"); abort(); }
     s->seeded = 1;
     philox4_t w = philox4x32_10(s->g, s->rep, 0u, PDA_SLOT_SEED, s->seed, s->epoch);
@@ -68,6 +98,7 @@ static unsigned long long curand(curandStateScrambledSobol64 *s)
 
 static float curand_uniform(curandStateScrambledSobol64 *s)
 {
+    if (s->sobol) return shim_u01((uint32_t)(sobol_next(s) >> 32));   /* _curand_uniform(ull), curand_uniform.h:84-89 */
     if (s->phase == 3 && s->bg_calls > 0) { /* fallback uniform of draw_P_B_Tr */
         philox4_t w = philox4x32_10(s->g, s->rep, s->step,
                                     s->bg_calls == 1 ? PDA_SLOT_BG_A : PDA_SLOT_BG_D, s->seed,
@@ -88,6 +119,7 @@ static float curand_uniform(curandStateScrambledSobol64 *s)
 
 static float curand_normal(curandStateScrambledSobol64 *s)
 {
+    if (s->sobol) return det_norm_icdf((uint32_t)(sobol_next(s) >> 32));   /* _curand_normal_icdf(ull) */
     if (s->phase != 3) { fprintf(stderr, "ref_shim: curand_normal out of order\n"); abort(); }
     philox4_t w = philox4x32_10(s->g, s->rep, s->step, PDA_SLOT_STEP, s->seed, s->epoch);
     s->step++;
@@ -99,14 +131,8 @@ static float curand_normal(curandStateScrambledSobol64 *s)
 /* cuRAND: curand_poisson(Sobol64, lambda) = _curand_poisson_ITR_double for lambda < 1000
  * (/usr/local/cuda/include/curand_poisson.h:436-463,546-551,759); that header is NVIDIA's,
  * restated here on det_exp so it replays bit-exactly. */
-static unsigned int curand_poisson(curandStateScrambledSobol64 *s, double lambda)
+static unsigned int shim_poisson_itr(uint64_t x, double lambda)
 {
-    if (s->phase != 3 || s->bg_calls > 1) { fprintf(stderr, "ref_shim: poisson out of order\n"); abort(); }
-    if (!(lambda < 1000.0)) { fprintf(stderr, "ref_shim: lambda >= 1000 outside contract\n"); abort(); }
-    s->bg_calls++;
-    philox4_t w = philox4x32_10(s->g, s->rep, s->step,
-                                s->bg_calls == 1 ? PDA_SLOT_BG_A : PDA_SLOT_BG_D, s->seed, s->epoch);
-    uint64_t x = ((uint64_t)w.v[0] << 32) | w.v[1];
     double u = (double)(x >> 11) * 1.1102230246251565e-16 + 2.7755575615628914e-17;
     double L, p = 1.0, q = 1.0;
     unsigned int k = 0;
@@ -123,6 +149,20 @@ static unsigned int curand_poisson(curandStateScrambledSobol64 *s, double lambda
         }
     } while ((double)pw < lambda);
     return k;
+}
+
+static unsigned int curand_poisson(curandStateScrambledSobol64 *s, double lambda)
+{
+    if (s->sobol) {
+        if (!(lambda < 1000.0)) { fprintf(stderr, "ref_shim: lambda >= 1000 outside contract\n"); abort(); }
+        return shim_poisson_itr(sobol_next(s), lambda);
+    }
+    if (s->phase != 3 || s->bg_calls > 1) { fprintf(stderr, "ref_shim: poisson out of order\n"); abort(); }
+    if (!(lambda < 1000.0)) { fprintf(stderr, "ref_shim: lambda >= 1000 outside contract\n"); abort(); }
+    s->bg_calls++;
+    philox4_t w = philox4x32_10(s->g, s->rep, s->step,
+                                s->bg_calls == 1 ? PDA_SLOT_BG_A : PDA_SLOT_BG_D, s->seed, s->epoch);
+    return shim_poisson_itr(((uint64_t)w.v[0] << 32) | w.v[1], lambda);
 }
 
 /* ---- libdevice stand-ins -------------------------------------------------------- */
@@ -212,6 +252,51 @@ void ref_mc_kernel(int64_t *start, int64_t *stop, int64_t *burst_ad, int64_t *bu
         mc_kernel(start, stop, burst_ad, burst_dd, istart, phCount, T, clk_p, bg_ad_rate,
                   bg_dd_rate, gpe, gpv, gpk, gpp_i2j, gpp, scratch.data(), N, s_n, q.data(),
                   st.data(), mcE, R);
+    }
+}
+
+/* The same with cuRAND's own generator: what the reference's class mc does on the GPU.
+ * mc::init_randstate (src/mc.cu:366-455) hands thread t the direction vectors and scramble
+ * constant of dimension t % 20000 of CURAND_SCRAMBLED_DIRECTION_VECTORS_64_JOEKUO6 (tables from
+ * libcurand's host API, passed in), setup_kernel starts every sequence at offset 1234 and seeds
+ * the xor128 stream from its first draw; the states persist over the `evals` evaluations
+ * (quirk Q8).  mcE: [evals][N*R].  Differences left against a GPU run: libdevice's
+ * logf/powf/erfcinvf/log/exp are a few ulp away from det_math.h. */
+void ref_mc_kernel_sobol(int64_t *start, int64_t *stop, int64_t *burst_ad, int64_t *burst_dd,
+                         int64_t *istart, int *phCount, float *T, float clk_p, float bg_ad_rate,
+                         float bg_dd_rate, float *gpe, float *gpv, float *gpk, float *gpp_i2j,
+                         float *gpp, int N, int s_n, int R, unsigned long long *dirvec20000x64,
+                         unsigned long long *scramble20000, int evals, float *mcE, int nthreads)
+{
+    int64_t NN = (int64_t)N * R;
+    std::vector<curandStateScrambledSobol64> q((size_t)NN);
+    std::vector<rk_state> st((size_t)NN);
+    std::vector<float> scratch((size_t)NN * (size_t)s_n);
+    std::vector<unsigned long long> scr((size_t)NN);
+    for (int64_t t = 0; t < NN; ++t) {
+        memset(&q[t], 0, sizeof(q[t]));
+        q[t].sobol = 1;
+        memset(&st[t], 0, sizeof(rk_state));
+        scr[t] = scramble20000[t % 20000];
+    }
+#ifdef _OPENMP
+    if (nthreads <= 0) nthreads = omp_get_max_threads();
+#endif
+    for (int ev = -1; ev < evals; ++ev) {
+#ifdef _OPENMP
+#pragma omp parallel for schedule(dynamic, 256) num_threads(nthreads)
+#endif
+        for (int64_t t = 0; t < NN; ++t) {
+            blockDim.x = 1;
+            threadIdx.x = 0;
+            blockIdx.x = (unsigned)t;
+            if (ev < 0)   /* setup_kernel reads sobolDirectionVectors + 64 * idx */
+                setup_kernel(st.data(), 0ul, (int)NN, dirvec20000x64 + 64 * (t % 20000) - 64 * t, scr.data(), q.data());
+            else
+                mc_kernel(start, stop, burst_ad, burst_dd, istart, phCount, T, clk_p, bg_ad_rate,
+                          bg_dd_rate, gpe, gpv, gpk, gpp_i2j, gpp, scratch.data(), N, s_n, q.data(),
+                          st.data(), mcE + (size_t)ev * (size_t)NN, R);
+        }
     }
 }
 
