@@ -20,6 +20,7 @@ GSM_FORCE_RAW64 = 4
 GSM_NO_INDEX = 8
 GSM_MODE_REPLAY = 0
 GSM_MODE_NORMAL = 1
+GSM_MODE_REFERENCE = 2
 PEER_HANDLE_BYTES = 128
 GSM_FLAG_STEP_CAP = 1
 GSM_FLAG_PEER_TIMEOUT = 2

@@ -68,6 +68,10 @@ static int nccl_load()
     g_nccl.h = h;
     return GSM_OK;
 }
+// cuRAND's host API hands out the Sobol tables mc::mc fetches (/root/reference/src/mc.cu:312-314);
+// only the reference-draws mode needs them
+static int load_sobol_tables(gsm_ctx* c);
+
 constexpr int kNcclUint64 = 5;  // ncclUint64 in nccl.h's ncclDataType_t
 constexpr int kNcclSum = 0;     // ncclSum
 
@@ -108,6 +112,11 @@ struct Slot {
     int32_t* d_steps = nullptr; int32_t* h_steps = nullptr;
     bool ran = false;
     uint32_t peer_seq = 0;   // evaluations exchanged on this slot so far
+    // reference-draws mode: the per-thread generators of the reference (devQStates / devStates)
+    ulonglong2* d_sob_state = nullptr;
+    uint4* d_xs_state = nullptr;
+    long long sob_NN = 0;      // threads the states were set up for (the reference re-seeds when N changes)
+    long long sob_cap = 0;
 };
 
 struct gsm_ctx {
@@ -147,6 +156,9 @@ struct gsm_ctx {
     unsigned long long* peer_map[kMaxPeers] = {nullptr};
     bool peer_ipc[kMaxPeers] = {false};
     uint32_t peer_timeout_ms = 20000;
+    // reference-draws mode: cuRAND's scrambled Sobol64 tables (20000 dimensions)
+    unsigned long long* d_sob_dv = nullptr;
+    unsigned long long* d_sob_sc = nullptr;
 };
 
 // what travels between ranks to map each other's symmetric block
@@ -317,6 +329,30 @@ static int build_observed(gsm_ctx* c)
     return GSM_OK;
 }
 
+static int load_sobol_tables(gsm_ctx* c)
+{
+    if (c->d_sob_dv) return GSM_OK;
+    void* h = dlopen("libcurand.so.10", RTLD_NOW);
+    if (!h) h = dlopen("libcurand.so", RTLD_NOW);
+    if (!h) return fail(GSM_ESTATE, "reference-draws mode needs libcurand (dlopen: %s)", dlerror());
+    typedef int (*GetDv)(unsigned long long (**)[64], int);
+    typedef int (*GetSc)(unsigned long long**);
+    GetDv get_dv = (GetDv)dlsym(h, "curandGetDirectionVectors64");
+    GetSc get_sc = (GetSc)dlsym(h, "curandGetScrambleConstants64");
+    if (!get_dv || !get_sc) return fail(GSM_ESTATE, "libcurand lacks the Sobol64 table getters");
+    unsigned long long (*dv)[64] = nullptr;
+    unsigned long long* sc = nullptr;
+    const int kScrambledJoeKuo6_64 = 104;   // CURAND_SCRAMBLED_DIRECTION_VECTORS_64_JOEKUO6 (curand.h)
+    if (get_dv(&dv, kScrambledJoeKuo6_64) != 0 || get_sc(&sc) != 0 || !dv || !sc)
+        return fail(GSM_ESTATE, "curandGetDirectionVectors64 / curandGetScrambleConstants64 failed");
+    CK(cudaSetDevice(c->devid));
+    CK(cudaMalloc((void**)&c->d_sob_dv, 20000 * 64 * sizeof(unsigned long long)));
+    CK(cudaMalloc((void**)&c->d_sob_sc, 20000 * sizeof(unsigned long long)));
+    CK(cudaMemcpy(c->d_sob_dv, dv, 20000 * 64 * sizeof(unsigned long long), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(c->d_sob_sc, sc, 20000 * sizeof(unsigned long long), cudaMemcpyHostToDevice));
+    return GSM_OK;
+}
+
 // ------------------------------------------------------------------------------------
 // C ABI
 // ------------------------------------------------------------------------------------
@@ -385,6 +421,7 @@ void gsm_destroy(gsm_ctx* c)
     for (Slot& s : c->slots) {
         cudaFreeHost(s.h_params); cudaFree(s.d_params);
         cudaFree(s.d_whist); cudaFree(s.d_counters); cudaFree(s.d_res); cudaFreeHost(s.h_res);
+        cudaFree(s.d_sob_state); cudaFree(s.d_xs_state);
         cudaFree(s.d_mcE); cudaFreeHost(s.h_mcE);
         cudaFree(s.d_cnt); cudaFreeHost(s.h_cnt);
         cudaFree(s.d_steps); cudaFreeHost(s.h_steps);
@@ -395,6 +432,7 @@ void gsm_destroy(gsm_ctx* c)
     cudaFree(c->d_bursts); cudaFree(c->d_pk); cudaFree(c->d_pm); cudaFree(c->d_nx); cudaFree(c->d_cw);
     cudaFree(c->d_ad); cudaFree(c->d_dd);
     cudaFree(c->d_sg); cudaFree(c->d_ohist);
+    cudaFree(c->d_sob_dv); cudaFree(c->d_sob_sc);
     cudaGetLastError();
     delete c;
 }
@@ -433,9 +471,15 @@ int gsm_set_seed(gsm_ctx* c, uint32_t seed)
 int gsm_set_mode(gsm_ctx* c, int mode)
 {
     if (!c) return fail(GSM_EINVAL, "null context");
-    if (mode != GSM_MODE_REPLAY && mode != GSM_MODE_NORMAL) return fail(GSM_EINVAL, "unknown mode %d", mode);
+    if (mode != GSM_MODE_REPLAY && mode != GSM_MODE_NORMAL && mode != GSM_MODE_REFERENCE)
+        return fail(GSM_EINVAL, "unknown mode %d", mode);
     if (mode != c->mode) {
         for (Slot& s : c->slots) CK(cudaStreamSynchronize(s.stream));
+        if (mode == GSM_MODE_REFERENCE) {
+            int r = load_sobol_tables(c);
+            if (r) return r;
+            for (Slot& s : c->slots) s.sob_NN = 0;   // a fresh mc: setup_kernel runs before the first evaluation
+        }
         c->mode = mode;
         if (c->inited) c->cfg = eval_launch_cfg(c->devid, c->layout, c->with_bg, c->nb, c->mode);
     }
@@ -661,7 +705,10 @@ int gsm_init_randstate(gsm_ctx* c, int, int sid)
 {
     int r = check_sid(c, sid);
     if (r) return r;
-    return GSM_OK;  // nothing to build: the draw epoch already advances with every run
+    // counter-based modes: nothing to build, the draw epoch already advances with every run.
+    // reference-draws mode: mc::init_randstate rebuilds the Sobol and xor128 states from scratch
+    if (c->mode == GSM_MODE_REFERENCE) c->slots[sid].sob_NN = 0;
+    return GSM_OK;
 }
 
 int gsm_set_params_buff(gsm_ctx* c, int, int, int sid) { return check_sid(c, sid); }
@@ -715,6 +762,26 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
     a.seed = c->seed; a.epoch0 = s.epoch;
     a.clk_p = c->clk_p; a.bg_ad_rate = c->bg_ad; a.bg_dd_rate = c->bg_dd;
 
+    if (c->mode == GSM_MODE_REFERENCE) {
+        if (s.P != 1) return fail(GSM_EINVAL, "reference-draws mode evaluates one vector per launch (the reference's thread = one (burst, repeat))");
+        if (c->peer_on || c->comm) return fail(GSM_ESTATE, "reference-draws mode does not combine with burst-split runs");
+        const long long NN = (long long)N * c->R;
+        if (NN > s.sob_cap) {
+            CK(cudaStreamSynchronize(s.stream));
+            if (s.d_sob_state) CK(cudaFree(s.d_sob_state));
+            if (s.d_xs_state) CK(cudaFree(s.d_xs_state));
+            s.d_sob_state = nullptr; s.d_xs_state = nullptr; s.sob_cap = 0;
+            CK(cudaMalloc((void**)&s.d_sob_state, (size_t)NN * sizeof(ulonglong2)));
+            CK(cudaMalloc((void**)&s.d_xs_state, (size_t)NN * sizeof(uint4)));
+            s.sob_cap = NN;
+        }
+        if (NN != s.sob_NN) {   // gpuWorker calls init_randstate when N changes (gpuWorker.cpp:74-77)
+            CK(launch_setup_ref(c->d_sob_dv, c->d_sob_sc, NN, s.d_sob_state, s.d_xs_state, s.stream));
+            c->launches += NN > 0 ? 1 : 0;
+            s.sob_NN = NN;
+        }
+        a.sob_dv = c->d_sob_dv; a.sob_state = s.d_sob_state; a.xs_state = s.d_xs_state;
+    }
     CK(cudaEventRecord(s.ev0, s.stream));
     if (s.P == 1 && !c->comm) {
         // one vector: it rides in the launch parameters (run_resident re-sends the same bytes)

@@ -1,5 +1,8 @@
 // pda_eval.cuh — the persistent evaluation kernel template, shared by the two translation
 // units that instantiate it:
+//   kMode: kModeReplay (0), kModeNormal (1, "kFast"), kModeReference (2, "kSobol": replay arithmetic
+//   on the reference's own generator — per-thread cuRAND scrambled Sobol64 sequences and a
+//   persistent xor128 stream, pda_kernels_ref.cu)
 //   pda_kernels.cu       kFast = false  replay mode: explicit-rounding arithmetic, FP64 binomial on
 //                                       the xor128 stream, compiled -fmad=false (bit-exact contract)
 //   pda_kernels_fast.cu  kFast = true   normal mode: FP32 arithmetic with hardware lg2/ex2/rcp and
@@ -13,6 +16,7 @@
 
 namespace pda {
 
+constexpr int kModeReplay = 0, kModeNormal = 1, kModeReference = 2;
 constexpr int kBlock = 256;
 constexpr int kChunkMax = 256;          // most consecutive samples a warp draws per ticket (EvalArgs::chunk)
 constexpr int kMaxBins = 1024;          // nb + 2 <= kMaxBins
@@ -96,7 +100,20 @@ struct Lane {
     int64_t bin0;
     int first, si;
     uint32_t step;
+    // reference-draws mode: position in the thread's Sobol64 sequence
+    unsigned long long sob_i, sob_x;
+    const unsigned long long* sob_dv;
 };
+
+// next 64-bit word of the thread's scrambled Sobol64 sequence (cuRAND's update: flip the
+// direction vector of the lowest zero bit of the index)
+__device__ __forceinline__ unsigned long long sobol_next(Lane& L)
+{
+    const unsigned long long r = L.sob_x;
+    L.sob_x ^= __ldg(L.sob_dv + (__ffsll((long long)~L.sob_i) - 1));
+    L.sob_i++;
+    return r;
+}
 
 __device__ __forceinline__ uint32_t lane_g(const EvalArgs& a, const Lane& L)
 {
@@ -192,7 +209,7 @@ __device__ __forceinline__ Window scan_indexed(const EvalArgs& a, const Lane& L,
 }
 
 // start a sample: burst record, binomial stream (role of setup_kernel, gen_rand.cuh:7-25)
-template <bool kFast>
+template <int kMode>
 __device__ __forceinline__ void lane_begin(Lane& L, const SmemParams& sp, const EvalArgs& a, uint32_t bl,
                                            uint32_t rep, uint32_t epoch)
 {
@@ -207,7 +224,17 @@ __device__ __forceinline__ void lane_begin(Lane& L, const SmemParams& sp, const 
     L.off4 = (uint32_t)r1.z;      // packed layouts; the raw layout re-reads its 64-bit offset
     L.scale = (uint32_t)r1.w;
     L.si = 0;
-    if (!kFast) {
+    constexpr bool kFast = kMode == kModeNormal;
+    if (kMode == kModeReference) {
+        // the reference's thread tidx = burst * R + repeat resumes its Sobol sequence and its
+        // xor128 stream where the previous evaluation left them (mc.cu:366-455, quirk Q8)
+        const size_t t = (size_t)bl * (size_t)a.R + rep;
+        const ulonglong2 st = a.sob_state[t];
+        L.sob_i = st.x; L.sob_x = st.y;
+        L.sob_dv = a.sob_dv + 64u * (unsigned)(t % 20000u);
+        const uint4 xs = a.xs_state[t];
+        L.xs.s0 = xs.x; L.xs.s1 = xs.y; L.xs.s2 = xs.z; L.xs.s3 = xs.w;
+    } else if (!kFast) {
         // replay mode: the binomial stream of the sample (draw contract); the
         // normal mode needs no per-sample block, its draws all come from the step blocks
         const u32x4 sd = philox4x32_10(lane_g(a, L), rep, 0u, kSlotSeed, a.seed, epoch);
@@ -219,13 +246,33 @@ __device__ __forceinline__ void lane_begin(Lane& L, const SmemParams& sp, const 
     L.step = 0;
 }
 
+// reference-draws mode: leave the generators where the next evaluation resumes them
+__device__ __forceinline__ void lane_save_reference(const Lane& L, const EvalArgs& a)
+{
+    const size_t t = (size_t)L.bl * (size_t)a.R + L.rep;
+    a.sob_state[t] = make_ulonglong2(L.sob_i, L.sob_x);
+    a.xs_state[t] = make_uint4(L.xs.s0, L.xs.s1, L.xs.s2, L.xs.s3);
+}
+
 // one dwell window (one trip of the reference's while loop, mc.cu:117-191)
-template <int kLayout, bool kBg, bool kFast>
+template <int kLayout, bool kBg, int kMode>
 __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const EvalArgs& a, uint32_t epoch)
 {
+    constexpr bool kFast = kMode == kModeNormal;
+    constexpr bool kSobol = kMode == kModeReference;
     const int n = sp.n;
     const uint32_t g = lane_g(a, L);
-    const u32x4 w = philox4x32_10(g, L.rep, L.step, kSlotStep, a.seed, epoch);
+    u32x4 w;
+    if (kSobol) {
+        // the reference's draw order: initial state (first step only), next state, dwell;
+        // the E draw and the background draws are taken further down, only when they happen
+        w.w = L.step == 0 ? (uint32_t)(sobol_next(L) >> 32) : 0u;
+        w.x = (uint32_t)(sobol_next(L) >> 32);
+        w.y = (uint32_t)(sobol_next(L) >> 32);
+        w.z = 0u;
+    } else {
+        w = philox4x32_10(g, L.rep, L.step, kSlotStep, a.seed, epoch);
+    }
     if (L.step == 0) {
         // initial state (mc.cu:110).  Replay: word 3 of the step-0 block (draw contract).  Normal:
         // the low bytes of the four words — the uniforms of this block are built from the top 24
@@ -279,6 +326,21 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
             sv = (float)poisson_fast(bw.z, t_diff * a.bg_dd_rate);
             const float bg_d = (sv <= rf_id) ? sv : floorf(rf_id * u01(bw.w));
             f_i = floorf(f_if - bg_d - bg_a + 0.5f);
+        } else if (kSobol) {
+            // draw_P_B_Tr (gen_rand.cuh:92-107): one 64-bit word per Poisson draw, a further
+            // word only when the draw exceeds the photons there are
+            const float t_diff = (float)(bin1 - L.bin0) * a.clk_p;
+            const float rf_ia = (1.0f - kDexDirAem) * (float)win.f_ia;
+            unsigned long long x = sobol_next(L);
+            uint32_t sv = poisson_itr((uint32_t)(x >> 32), (uint32_t)x, (double)(t_diff * a.bg_ad_rate));
+            const float bg_a = ((float)(int32_t)sv <= rf_ia) ? (float)(int32_t)sv
+                                                             : floorf(rf_ia * u01((uint32_t)(sobol_next(L) >> 32)));
+            const float rf_id = (kGamma - kDch2Ach) * (float)win.f_id;
+            x = sobol_next(L);
+            sv = poisson_itr((uint32_t)(x >> 32), (uint32_t)x, (double)(t_diff * a.bg_dd_rate));
+            const float bg_d = ((float)(int32_t)sv <= rf_id) ? (float)(int32_t)sv
+                                                             : floorf(rf_id * u01((uint32_t)(sobol_next(L) >> 32)));
+            f_i = floorf(f_if - bg_d - bg_a + 0.5f);
         } else {
             const float t_diff = (float)(bin1 - L.bin0) * a.clk_p;
             const float rf_ia = (1.0f - kDexDirAem) * (float)win.f_ia;
@@ -298,6 +360,7 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
             const float de = __fdividef(1.0f, fmaf(x2 * x2, x2, 1.0f));
             ai = binomial_fast((int)f_i, de, w.w, g, L.rep, L.step, a.seed, epoch);
         } else {
+            if (kSobol) w.z = (uint32_t)(sobol_next(L) >> 32);
             const float rd = det_norm_icdf(w.z) * sp.v[si] + sp.rootE[si];
             const float de = 1.0f / (1.0f + det_pow6f(rd / kR0));
             ai = (int)binomial(L.xs, (int)f_i, (double)de);
@@ -476,7 +539,7 @@ __device__ __forceinline__ void peer_exchange_block(const EvalArgs& a)
 #ifndef PDA_MIN_BLOCKS
 #define PDA_MIN_BLOCKS 4
 #endif
-template <int kLayout, bool kBg, bool kFast>
+template <int kLayout, bool kBg, int kMode>
 __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const __grid_constant__ EvalArgs a)
 {
     constexpr int kWarps = kBlock / 32;
@@ -583,7 +646,7 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
             if (take) {
                 const uint32_t x = c_rep + (uint32_t)rank;
                 const uint32_t q = smallR ? __umulhi(x, magicR) : x / (uint32_t)a.R;
-                lane_begin<kFast>(L, sp, a, c_bl + q, x - q * (uint32_t)a.R, wc.epoch);
+                lane_begin<kMode>(L, sp, a, c_bl + q, x - q * (uint32_t)a.R, wc.epoch);
                 active = true;
             }
             __syncwarp();
@@ -599,6 +662,10 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
             // a burst of zero duration never enters the reference's while loop: E = 0
             const bool dead = take && !(L.T > 0.0f);
             if (dead) {
+                if (kMode == kModeReference) {   // the initial-state draw precedes the loop (mc.cu:110)
+                    (void)sobol_next(L);
+                    lane_save_reference(L, a);
+                }
                 const size_t oi = (size_t)wc.cur_p * (size_t)per_p + (size_t)L.bl * (size_t)a.R + L.rep;
                 if (a.mcE) a.mcE[oi] = 0.0f;
                 if (a.sum_ai) a.sum_ai[oi] = 0;
@@ -614,13 +681,14 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
 
         // ---- one dwell window for every active lane -------------------------------------
         if (active) {
-            lane_step<kLayout, kBg, kFast>(L, sp, a, wc.epoch);
+            lane_step<kLayout, kBg, kMode>(L, sp, a, wc.epoch);
             bool fin = !(L.T > L.spent);
             if (!fin && L.step >= kStepCap) {
                 atomicOr(a.counters + 2, 1ull);
                 fin = true;
             }
             if (fin) {
+                if (kMode == kModeReference) lane_save_reference(L, a);
                 // IEEE division in both modes: E takes few distinct values (small integer
                 // counts), so a 1-ulp difference would move whole atoms of the distribution.
                 // 0 / F = +0 is spelled out: a zero numerator (no acceptor photon drawn — a
@@ -675,26 +743,26 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
 // ------------------------------------------------------------------------------------
 // launch helpers, instantiated once per translation unit (kFast fixed by the unit)
 // ------------------------------------------------------------------------------------
-template <int kLayout, bool kBg, bool kFast>
+template <int kLayout, bool kBg, int kMode>
 static int resident_blocks(size_t dyn)
 {
     int nb = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, pda_eval_kernel<kLayout, kBg, kFast>, kBlock, dyn);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, pda_eval_kernel<kLayout, kBg, kMode>, kBlock, dyn);
     return nb < 1 ? 1 : nb;
 }
 
 static inline size_t eval_dyn_smem(int nb) { return (size_t)(kBlock / 32) * (size_t)(nb + 2) * sizeof(unsigned int); }
 
-template <bool kFast>
+template <int kMode>
 static LaunchCfg eval_launch_cfg_t(int device, int layout, bool with_bg, int nb)
 {
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     const size_t dyn = eval_dyn_smem(nb);
     int per;
-    if (layout == 0) per = with_bg ? resident_blocks<0, true, kFast>(dyn) : resident_blocks<0, false, kFast>(dyn);
-    else if (layout == 1) per = with_bg ? resident_blocks<1, true, kFast>(dyn) : resident_blocks<1, false, kFast>(dyn);
-    else per = with_bg ? resident_blocks<2, true, kFast>(dyn) : resident_blocks<2, false, kFast>(dyn);
+    if (layout == 0) per = with_bg ? resident_blocks<0, true, kMode>(dyn) : resident_blocks<0, false, kMode>(dyn);
+    else if (layout == 1) per = with_bg ? resident_blocks<1, true, kMode>(dyn) : resident_blocks<1, false, kMode>(dyn);
+    else per = with_bg ? resident_blocks<2, true, kMode>(dyn) : resident_blocks<2, false, kMode>(dyn);
     return LaunchCfg{sms * per, kBlock};
 }
 
@@ -719,14 +787,14 @@ static inline void shape_launch(EvalArgs& a, LaunchCfg& cfg)
     if (blocks < cfg.grid) cfg.grid = (int)blocks;
 }
 
-template <bool kFast>
+template <int kMode>
 static cudaError_t launch_eval_t(const EvalArgs& a_in, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s)
 {
     if (a_in.nb + 2 > kMaxBins) return cudaErrorInvalidValue;
     EvalArgs a = a_in;
     shape_launch(a, cfg);
     const size_t dyn = eval_dyn_smem(a.nb);
-#define PDA_LAUNCH(LAY, BG) pda_eval_kernel<LAY, BG, kFast><<<cfg.grid, cfg.block, dyn, s>>>(a)
+#define PDA_LAUNCH(LAY, BG) pda_eval_kernel<LAY, BG, kMode><<<cfg.grid, cfg.block, dyn, s>>>(a)
     if (layout == 0) { if (with_bg) PDA_LAUNCH(0, true); else PDA_LAUNCH(0, false); }
     else if (layout == 1) { if (with_bg) PDA_LAUNCH(1, true); else PDA_LAUNCH(1, false); }
     else { if (with_bg) PDA_LAUNCH(2, true); else PDA_LAUNCH(2, false); }

@@ -207,14 +207,16 @@ __global__ void pda_probe_kernel(const ProbeArgs a)
 // ------------------------------------------------------------------------------------
 LaunchCfg eval_launch_cfg(int device, int layout, bool with_bg, int nb, int mode)
 {
+    if (mode == 2) return eval_launch_cfg_ref(device, layout, with_bg, nb);
     return mode == 1 ? eval_launch_cfg_fast(device, layout, with_bg, nb)
-                     : eval_launch_cfg_t<false>(device, layout, with_bg, nb);
+                     : eval_launch_cfg_t<kModeReplay>(device, layout, with_bg, nb);
 }
 
 cudaError_t launch_eval(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s, int mode)
 {
+    if (mode == 2) return launch_eval_ref(a, layout, with_bg, cfg, s);
     return mode == 1 ? launch_eval_fast(a, layout, with_bg, cfg, s)
-                     : launch_eval_t<false>(a, layout, with_bg, cfg, s);
+                     : launch_eval_t<kModeReplay>(a, layout, with_bg, cfg, s);
 }
 
 cudaError_t launch_finalize(const EvalArgs& a, cudaStream_t s)

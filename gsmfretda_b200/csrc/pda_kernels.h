@@ -87,6 +87,10 @@ struct EvalArgs {
     uint32_t epoch0;           // parameter vector p draws with epoch0 + p
     float clk_p, bg_ad_rate, bg_dd_rate;
     PeerArgs peer;
+    // reference-draws mode (GSM_MODE_REFERENCE): the reference's per-thread generators
+    const unsigned long long* sob_dv;   // [20000][64] direction vectors (CURAND_SCRAMBLED_DIRECTION_VECTORS_64_JOEKUO6)
+    ulonglong2* sob_state;              // [N*R] (index i, word x) of every thread's sequence
+    uint4* xs_state;                    // [N*R] xor128 state of rk_state
     // single-vector launches carry the vector in the launch parameters: no upload on the stream
     int32_t use_inl;
     ParamRaw inl;
@@ -103,6 +107,12 @@ struct LaunchCfg {
 // mode: 0 replay (bit-exact draw contract), 1 normal (FP32 fast arithmetic)
 LaunchCfg eval_launch_cfg(int device, int layout, bool with_bg, int nb, int mode);
 cudaError_t launch_eval(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s, int mode);
+// reference-draws instantiation (pda_kernels_ref.cu) and the role of setup_kernel (gen_rand.cuh:7-25):
+// thread t starts dimension t % 20000 at offset 1234 and seeds its xor128 stream from the first word
+LaunchCfg eval_launch_cfg_ref(int device, int layout, bool with_bg, int nb);
+cudaError_t launch_eval_ref(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s);
+cudaError_t launch_setup_ref(const unsigned long long* dv, const unsigned long long* scramble, long long NN,
+                             ulonglong2* sob_state, uint4* xs_state, cudaStream_t s);
 // the normal-mode instantiation lives in its own translation unit (pda_kernels_fast.cu, fmad on)
 LaunchCfg eval_launch_cfg_fast(int device, int layout, bool with_bg, int nb);
 cudaError_t launch_eval_fast(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s);

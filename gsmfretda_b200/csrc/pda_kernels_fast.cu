@@ -11,12 +11,12 @@ namespace pda {
 
 LaunchCfg eval_launch_cfg_fast(int device, int layout, bool with_bg, int nb)
 {
-    return eval_launch_cfg_t<true>(device, layout, with_bg, nb);
+    return eval_launch_cfg_t<kModeNormal>(device, layout, with_bg, nb);
 }
 
 cudaError_t launch_eval_fast(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s)
 {
-    return launch_eval_t<true>(a, layout, with_bg, cfg, s);
+    return launch_eval_t<kModeNormal>(a, layout, with_bg, cfg, s);
 }
 
 }  // namespace pda

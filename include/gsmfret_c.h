@@ -82,6 +82,14 @@ int gsm_set_seed(gsm_ctx* ctx, uint32_t seed);
  * Results of either mode are a pure function of (data, parameters, seed, epoch). */
 #define GSM_MODE_REPLAY 0
 #define GSM_MODE_NORMAL 1
+/*   GSM_MODE_REFERENCE  replay arithmetic on the REFERENCE'S OWN generators: one cuRAND scrambled
+ *                    Sobol64 sequence per (burst, repeat) thread (dimension tidx % 20000, offset 1234,
+ *                    mc.cu:366-455, gen_rand.cuh:7-25) drawn in the reference's order, and its xor128
+ *                    stream; both persist across evaluations of a stream slot and restart when N
+ *                    changes, as gpuWorker drives them (gpuWorker.cpp:74-77).  Per-sample results,
+ *                    histogram and chi-square then equal the reference's class mc bit for bit.
+ *                    One vector per launch; needs libcurand (tables only) at run time. */
+#define GSM_MODE_REFERENCE 2
 int gsm_set_mode(gsm_ctx* ctx, int mode);
 int gsm_mode(const gsm_ctx* ctx);
 /* fretHistNum / leftPad of streamWorker (streamWorker.cpp:41,62-70; main.cpp:155); defaults 200, 2 */
