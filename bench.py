@@ -231,7 +231,7 @@ def main():
     ap.add_argument("--bursts", type=int, default=None, help="override bursts per GPU")
     ap.add_argument("--repeats", type=int, default=None)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--mode", default="replay", choices=["replay", "normal"],
+    ap.add_argument("--mode", default="replay", choices=["replay", "normal", "reference"],
                     help="replay: bit-exact draw contract (FP64 binomial); normal: FP32 fast arithmetic")
     ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
                     help="burst-split histogram reduction at N > 1: peer = fused into the evaluation kernel "
@@ -280,7 +280,8 @@ def main():
     mc.set_reSampleTimes(R)
     mc.set_seed(SEED)
     mc.set_hist(NB, LEFT_PAD)
-    mc.set_mode(capi.GSM_MODE_NORMAL if args.mode == "normal" else capi.GSM_MODE_REPLAY)
+    MODES = {"replay": capi.GSM_MODE_REPLAY, "normal": capi.GSM_MODE_NORMAL, "reference": capi.GSM_MODE_REFERENCE}
+    mc.set_mode(MODES[args.mode])
     mc.init_bursts(b, g_offset=0 if population else rank * B)
     if world > 1 and not population:
         if args.collective == "nccl":
@@ -361,7 +362,7 @@ def main():
 
     # the same step in the other arithmetic (replay <-> normal), device-timed, for the record
     other = "normal" if args.mode == "replay" else "replay"
-    mc.set_mode(capi.GSM_MODE_NORMAL if other == "normal" else capi.GSM_MODE_REPLAY)
+    mc.set_mode(MODES[other])
     k_other = max(3, min(args.steps, 50))
     for _ in range(3):
         step_resident()
@@ -391,7 +392,8 @@ def main():
             "metric": "burst-samples/s", "value": value, "unit": "burst-samples/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "strong" if population else "weak", "vs_baseline": None,
-            "dtype": ("f32 walk + f64 binomial (replay arithmetic), u32/u64 histogram" if args.mode == "replay"
+            "dtype": ("f32 walk + f64 binomial (replay arithmetic), u32/u64 histogram" if args.mode == "replay" else
+                      "f32 walk + f64 binomial (replay arithmetic) on the reference's Sobol64/xor128 generators" if args.mode == "reference"
                       else "f32 (normal mode: hardware lg2/ex2/rcp, f32 binomial inversion), u32/u64 histogram"),
             "mode": args.mode,
             "data": "synthetic",

@@ -6,7 +6,8 @@
 //
 // Additions (long options only, none changes the defaults):
 //   --resample-times R   Monte-Carlo repeats per burst (reference: fixed 4, mc.hpp:88)
-//   --mode replay|normal evaluation arithmetic; default normal
+//   --mode replay|normal|reference evaluation arithmetic / draw source; default normal;
+//          reference = the reference's own Sobol64 + xor128 generators: results equal the reference's bit for bit
 //   --seed S             seed of the counter-based generator
 //   --epoch-from-idx     draw stream of an evaluation = f(seed, params_idx) instead of the order
 //                        in which streams happened to evaluate: results reproducible whatever
@@ -49,7 +50,7 @@ static void usage()
         "  -p, --parameters=FLOAT    Calculate with the parameters. Give them like -p 0.34,0.56,455,673,2,4\n"
         "  -I, --pid=STRING          Appoint a pid file\n"
         "      --resample-times=INT  Monte-Carlo repeats per burst  (default=`4')\n"
-        "      --mode=STRING         replay|normal  (default=`normal')\n"
+        "      --mode=STRING         replay|normal|reference  (default=`normal')\n"
         "      --seed=INT            generator seed\n"
         "      --epoch-from-idx      reproducible draws per parameter index  (default=off)\n"
         "      --host-hist           host histogram and chi-square, as the reference  (default=off)\n";
@@ -142,8 +143,8 @@ int main(int argc, char* argv[])
         return EXIT_FAILURE;
     }
     const std::string H5FILE_NAME = input.empty() ? argv[optind] : input;
-    if (mode != "replay" && mode != "normal") {
-        std::cout << "--mode is replay or normal" << std::endl;
+    if (mode != "replay" && mode != "normal" && mode != "reference") {
+        std::cout << "--mode is replay, normal or reference" << std::endl;
         return EXIT_FAILURE;
     }
     std::cout << "Using " << H5FILE_NAME << std::endl;
@@ -177,7 +178,7 @@ int main(int argc, char* argv[])
     std::cout << "streamNum: " << streamNum << std::endl;
     if (streamNum <= 0) return EXIT_FAILURE;
     pdamc.set_reSampleTimes_exact(R);
-    GSM_CHECK_RETURN(gsm_set_mode(pdamc.handle(), mode == "replay" ? GSM_MODE_REPLAY : GSM_MODE_NORMAL));
+    GSM_CHECK_RETURN(gsm_set_mode(pdamc.handle(), mode == "replay" ? GSM_MODE_REPLAY : (mode == "reference" ? GSM_MODE_REFERENCE : GSM_MODE_NORMAL)));
     pdamc.init_data_gpu(istart, start, stop, phCount, (long)times_ms.size(), burst_ad, burst_dd, T_burst_duration,
                         SgDivSr, clk_p, bg_ad_rate, bg_dd_rate);
 
