@@ -193,6 +193,32 @@ def cpu_leg(w, sample_bursts, R, seconds_hint=12.0):
     return out
 
 
+def reference_on_gpu(cfg, bursts, timeout=90.0):
+    """Second baseline of SURVEY.md 8(d): the reference's own `class mc` (unmodified mc.cu built
+    for sm_100a, oracle/_ref/libref_gpu.so) through its own API on this GPU, in a process of its
+    own (its destructor resets the device), at the reference's default reSampleTimes = 4."""
+    exe = os.path.join(ROOT, "oracle", "refgpu_run.py")
+    if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libref_gpu.so")):
+        return {"unavailable": "oracle/_ref/libref_gpu.so not built"}
+    try:
+        r = subprocess.run([sys.executable, exe, "--cfg", str(cfg), "--bursts", str(bursts), "--repeats", "4",
+                            "--evals", "1", "--time", "10"], capture_output=True, text=True, timeout=timeout)
+        for ln in r.stdout.splitlines():
+            if ln.startswith("{"):
+                d = json.loads(ln)
+                return {"value": d["burst_samples_per_s_with_host_hist"], "unit": "burst-samples/s",
+                        "kernel_plus_d2h_only": d["burst_samples_per_s_kernel_d2h"],
+                        "ms_per_evaluation": 1e3 * (d["kernel_plus_d2h_s_per_eval"] + d["host_hist_s_per_eval"]),
+                        "sample": f"{d['evals_timed']} evaluations of {d['bursts']} bursts x {d['repeats']} repeats "
+                                  f"(the reference's default reSampleTimes) through mc::run_kernel + D2H of N*R floats "
+                                  f"+ host histogram (numpy bincount standing in for boost::histogram)"}
+        return {"unavailable": f"no result line (rc {r.returncode})"}
+    except subprocess.TimeoutExpired:
+        return {"unavailable": f"the reference did not return within {timeout:.0f} s"}
+    except Exception as e:   # noqa: BLE001
+        return {"unavailable": repr(e)}
+
+
 def run_reference(args, w, rank):
     if rank != 0:
         return
@@ -435,8 +461,14 @@ def main():
         if not args.no_cpu:
             cb = cpu_leg(w, min(B, 100000), R, seconds_hint=12.0)
             out["cpu_baseline"] = cb
+        mc.close()
+        mc = None
+        if not args.no_cpu and world == 1:
+            torch.cuda.synchronize()
+            out["cpu_baseline"]["reference_on_gpu"] = reference_on_gpu(args.cfg, min(B, 100000))
         print(json.dumps(out), flush=True)
-    mc.close()
+    if mc is not None:
+        mc.close()
     if world > 1:
         dist.destroy_process_group()
 
