@@ -137,3 +137,17 @@ def test_normal_mode_node_is_statistically_the_same(world):
             assert np.abs(sh / sh.sum() - h[:NB] / h[:NB].sum()).sum() < 0.5
     finally:
         srv.close()
+
+
+def test_node_in_reference_mode_equals_the_reference(world, ref, oracle):
+    """gSMFRETda --mode reference from an HDF5 file: the chi-square printed for one vector is the
+    one streamWorker would compute from the reference's own mc_kernel samples (host build of the
+    reference sources on cuRAND's Sobol draws = the reference's GPU run, test_reference_gpu_golden.py)."""
+    v = world["vecs"][2]
+    r = subprocess.run([NODE, "-i", os.path.join(H5, "from_bin.h5"), "-s", "1", "--mode", "reference", "--resample-times",
+                        str(R), "-p", ",".join(repr(x) for x in v)], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    chi2 = float([l for l in r.stdout.split("\n") if l.startswith("chi2:")][0].split()[1])
+    e = ref.mc_kernel_sobol(world["b"], 2, np.array(v, np.float32), R, evals=1)[0]
+    want = oracle.chi2(world["ohist"], oracle.hist(e, NB), NB, R, LEFT_PAD, 2)
+    assert np.float32(chi2) == np.float32(want), (chi2, want)
