@@ -441,6 +441,9 @@ def main():
                     "h2d_bytes_per_step": 612 * P_local, "d2h_bytes_per_step": 16 + P_local * ((NB + 2) * 8 + 4),
                     "param_evals_per_s": args.steps * P_job / e2e_s,
                     "ms_per_step": 1e3 * e2e_s / args.steps,
+                    "transport": ("vectors by cudaMemcpyAsync from pinned memory, results by one DMA to pinned memory" if population else
+                                  "the 612-byte vector rides in the launch parameters, the kernel's last block writes "
+                                  "flags | histogram | chi-square into mapped pinned host memory: no copy on the stream"),
                     "api": ("Mc.run_batch/streamQuery + chi2v()/hist()" if population else
                             "Mc.set_nstates/set_params/setBurstBd/run_kernel/streamQuery + chi2()/hist()")},
             "gpu_launches": int(launches),
