@@ -126,6 +126,23 @@ class Oracle:
                                  C.byref(st), nthreads)
         return dict(mcE=mcE, sum_ai=sa, F=F, n_steps=ns)
 
+    def eval_sobol(self, b, n, args, R, evals=1, N=None, nthreads=0) -> np.ndarray:
+        """The restatement on the reference's own generators (Sobol64 + xor128, persistent over
+        `evals` evaluations) -> mcE[evals, N*R]: what the reference's class mc computes on the GPU."""
+        N = b.n_bursts if N is None else N
+        prm = self.params(n, args)
+        assert prm is not None, "bad parameter vector"
+        bt = self.bursts_t(b)
+        dv, sc = sobol_tables()
+        out = np.zeros((evals, N * R), np.float32)
+        u64p = C.POINTER(C.c_uint64)
+        self.lib.pda_oracle_eval_sobol.restype = None
+        self.lib.pda_oracle_eval_sobol.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int64, u64p, u64p,
+                                                   C.c_int, _f32p, C.c_int]
+        self.lib.pda_oracle_eval_sobol(C.byref(bt), C.byref(prm), R, N, dv.ctypes.data_as(u64p),
+                                       sc.ctypes.data_as(u64p), evals, out.ctypes.data_as(_f32p), nthreads)
+        return out
+
     def hist(self, x, nb) -> np.ndarray:
         x = np.ascontiguousarray(x, np.float32)
         h = np.zeros(nb + 2, np.uint64)

@@ -306,10 +306,31 @@ int pda_oracle_params(int n, const float *args, int n_args, pda_params_t *out)
     return 1;
 }
 
-/* ---- one thread of mc_kernel, src/mc.cu:92-196 --------------------------------- */
+/* ---- second draw source: the reference's own generators -------------------------
+ * One cuRAND scrambled Sobol64 sequence per thread (state i/x + 64 direction vectors, gray-code
+ * update: curand_kernel.h:1582-1591) consumed in the reference's call order, and the thread's
+ * xor128 stream; both persist from one evaluation to the next (src/mc.cu:366-455, quirk Q8). */
+typedef struct {
+    uint64_t i, x;
+    const uint64_t *dv;
+    uint32_t xs[4];
+} sobol_thread_t;
+
+static inline uint64_t sobol_next(sobol_thread_t *s)
+{
+    uint64_t r = s->x;
+    s->x ^= s->dv[__builtin_ctzll(~s->i)];
+    s->i++;
+    return r;
+}
+
+/* ---- one thread of mc_kernel, src/mc.cu:92-196 ---------------------------------
+ * S == NULL: the draw contract (Philox words keyed by burst, repeat, step, slot);
+ * S != NULL: the reference's Sobol64 + xor128 generators, drawn where the reference draws. */
 static void eval_sample(const pda_bursts_t *bd, const pda_params_t *prm, int64_t idx,
                         uint32_t g, uint32_t rep, uint32_t seed, uint32_t epoch,
-                        float *o_mcE, int64_t *o_sum, float *o_F, int32_t *o_steps)
+                        float *o_mcE, int64_t *o_sum, float *o_F, int32_t *o_steps,
+                        sobol_thread_t *S)
 {
     const int n = prm->n;
     const int ph = bd->ph_count[idx];
@@ -322,11 +343,15 @@ static void eval_sample(const pda_bursts_t *bd, const pda_params_t *prm, int64_t
     /* draws of step 0; the xor128 stream is seeded like setup_kernel seeds rk_state
      * from one 64-bit draw (gen_rand.cuh:19-21) */
     uint32_t xs[4];
-    {
+    philox4_t w = {{0u, 0u, 0u, 0u}};
+    if (S) {
+        memcpy(xs, S->xs, sizeof(xs));
+        w.v[3] = (uint32_t)(sobol_next(S) >> 32); /* drawDisIdx before the loop, mc.cu:110 */
+    } else {
         philox4_t sd = philox4x32_10(g, rep, 0u, PDA_SLOT_SEED, seed, epoch);
         rk_seed((uint64_t)sd.v[0] | ((uint64_t)sd.v[1] << 32), xs);
+        w = philox4x32_10(g, rep, 0u, PDA_SLOT_STEP, seed, epoch);
     }
-    philox4_t w = philox4x32_10(g, rep, 0u, PDA_SLOT_STEP, seed, epoch);
 
     float F = 0.0f, acc = 0.0f, spent = 0.0f;
     int64_t sum_ai = 0;
@@ -335,7 +360,12 @@ static void eval_sample(const pda_bursts_t *bd, const pda_params_t *prm, int64_t
     int first = 0;
     uint32_t step = 0;
     while (T > spent) { /* mc.cu:117 */
-        if (step) w = philox4x32_10(g, rep, step, PDA_SLOT_STEP, seed, epoch);
+        if (S) {
+            w.v[0] = (uint32_t)(sobol_next(S) >> 32); /* drawJ_Si2Sj */
+            w.v[1] = (uint32_t)(sobol_next(S) >> 32); /* drawTau */
+        } else if (step) {
+            w = philox4x32_10(g, rep, step, PDA_SLOT_STEP, seed, epoch);
+        }
         int sj = draw_j(prm->P_i2j, n, si, u01(w.v[0]));      /* mc.cu:118 */
         float st = draw_tau(prm->K[sj + si * n], u01(w.v[1])); /* mc.cu:122 */
         spent = spent + st;
@@ -358,17 +388,25 @@ static void eval_sample(const pda_bursts_t *bd, const pda_params_t *prm, int64_t
                 } else {
                     float t_diff = (float)(bin1 - bin0) * clk_p;
                     float rf_ia = (1.0f - PDA_DEXDIRAEM) * (float)f_ia;
-                    philox4_t ba = philox4x32_10(g, rep, step, PDA_SLOT_BG_A, seed, epoch);
+                    /* draw_P_B_Tr: one word per Poisson draw, a fall-back uniform only when the
+                     * draw exceeds the photons there are (gen_rand.cuh:92-107) */
+                    philox4_t ba = {{0u, 0u, 0u, 0u}}, bq = {{0u, 0u, 0u, 0u}};
+                    if (S) { uint64_t x = sobol_next(S); ba.v[0] = (uint32_t)(x >> 32); ba.v[1] = (uint32_t)x; }
+                    else ba = philox4x32_10(g, rep, step, PDA_SLOT_BG_A, seed, epoch);
                     uint32_t sv = poisson_itr(ba.v[0], ba.v[1], (double)(t_diff * bd->bg_ad_rate));
-                    float bg_a = ((float)(int32_t)sv <= rf_ia) ? (float)(int32_t)sv
-                                                               : floorf(rf_ia * u01(ba.v[2]));
+                    float bg_a;
+                    if ((float)(int32_t)sv <= rf_ia) bg_a = (float)(int32_t)sv;
+                    else bg_a = floorf(rf_ia * u01(S ? (uint32_t)(sobol_next(S) >> 32) : ba.v[2]));
                     float rf_id = (PDA_GAMMA - PDA_DCH2ACH) * (float)f_id;
-                    philox4_t bq = philox4x32_10(g, rep, step, PDA_SLOT_BG_D, seed, epoch);
+                    if (S) { uint64_t x = sobol_next(S); bq.v[0] = (uint32_t)(x >> 32); bq.v[1] = (uint32_t)x; }
+                    else bq = philox4x32_10(g, rep, step, PDA_SLOT_BG_D, seed, epoch);
                     sv = poisson_itr(bq.v[0], bq.v[1], (double)(t_diff * bd->bg_dd_rate));
-                    float bg_d = ((float)(int32_t)sv <= rf_id) ? (float)(int32_t)sv
-                                                               : floorf(rf_id * u01(bq.v[2]));
+                    float bg_d;
+                    if ((float)(int32_t)sv <= rf_id) bg_d = (float)(int32_t)sv;
+                    else bg_d = floorf(rf_id * u01(S ? (uint32_t)(sobol_next(S) >> 32) : bq.v[2]));
                     f_i = floorf(f_if - bg_d - bg_a + 0.5f);
                 }
+                if (S) w.v[2] = (uint32_t)(sobol_next(S) >> 32);             /* curand_normal in drawE */
                 float de = draw_e(prm->E[si], PDA_R0, prm->v[si], w.v[2]); /* mc.cu:167 */
                 ai = rk_binomial(xs, (int)f_i, (double)de);                /* mc.cu:168 */
                 break;
@@ -389,6 +427,7 @@ static void eval_sample(const pda_bursts_t *bd, const pda_params_t *prm, int64_t
     if (o_sum) *o_sum = sum_ai;
     if (o_F) *o_F = F;
     if (o_steps) *o_steps = (int32_t)step;
+    if (S) memcpy(S->xs, xs, sizeof(xs));
 }
 
 /* ---- boost::histogram regular axis index, 3rdparty/src/boost/libs/histogram/include/
@@ -443,8 +482,42 @@ void pda_oracle_eval(const pda_bursts_t *bursts, const pda_params_t *prm, int R,
         uint32_t rep = (uint32_t)(t % R);
         eval_sample(bursts, prm, b, (uint32_t)(b + g_offset), rep, seed, epoch,
                     out->mcE ? out->mcE + t : NULL, out->sum_ai ? out->sum_ai + t : NULL,
-                    out->F ? out->F + t : NULL, out->n_steps ? out->n_steps + t : NULL);
+                    out->F ? out->F + t : NULL, out->n_steps ? out->n_steps + t : NULL, NULL);
     }
+}
+
+/* The reference's generators: thread t = burst * R + repeat takes dimension t % 20000 of
+ * CURAND_SCRAMBLED_DIRECTION_VECTORS_64_JOEKUO6 at offset 1234 and seeds its xor128 stream from the
+ * first word (setup_kernel, gen_rand.cuh:7-25; mc::init_randstate, mc.cu:366-455); `evals`
+ * evaluations run on the persistent states.  mcE: [evals][N*R].  Tables from libcurand's host API. */
+void pda_oracle_eval_sobol(const pda_bursts_t *bursts, const pda_params_t *prm, int R, int64_t N,
+                           const uint64_t *dirvec20000x64, const uint64_t *scramble20000,
+                           int evals, float *mcE, int nthreads)
+{
+    int64_t total = N * (int64_t)R;
+    sobol_thread_t *st = (sobol_thread_t *)malloc((size_t)(total > 0 ? total : 1) * sizeof(sobol_thread_t));
+    for (int64_t t = 0; t < total; ++t) {
+        sobol_thread_t *s = &st[t];
+        s->dv = dirvec20000x64 + 64 * (t % 20000);
+        s->i = 1234;
+        s->x = scramble20000[t % 20000];
+        uint64_t gray = s->i ^ (s->i >> 1);
+        for (int k = 0; k < 64; ++k)
+            if (gray & (1ull << k)) s->x ^= s->dv[k];
+        rk_seed(sobol_next(s), s->xs);
+    }
+#ifdef _OPENMP
+    if (nthreads <= 0) nthreads = omp_get_max_threads();
+#endif
+    for (int ev = 0; ev < evals; ++ev) {
+#ifdef _OPENMP
+#pragma omp parallel for schedule(dynamic, 256) num_threads(nthreads)
+#endif
+        for (int64_t t = 0; t < total; ++t)
+            eval_sample(bursts, prm, t / R, 0u, 0u, 0u, 0u, mcE + (size_t)ev * (size_t)total + t, NULL, NULL,
+                        NULL, &st[t]);
+    }
+    free(st);
 }
 
 float pda_oracle_eval_chi2(const pda_bursts_t *bursts, const pda_params_t *prm, int R,
@@ -467,7 +540,7 @@ float pda_oracle_eval_chi2(const pda_bursts_t *bursts, const pda_params_t *prm, 
             int64_t b = b0 + t / R;
             float e;
             eval_sample(bursts, prm, b, (uint32_t)(b + g_offset), (uint32_t)(t % R), seed,
-                        epoch, &e, NULL, NULL, NULL);
+                        epoch, &e, NULL, NULL, NULL, NULL);
             local[hist_index(e, nb)]++;
         }
 #ifdef _OPENMP

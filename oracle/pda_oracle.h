@@ -60,6 +60,15 @@ void pda_oracle_eval(const pda_bursts_t *bursts, const pda_params_t *prm, int R,
                      uint32_t seed, uint32_t epoch, int64_t b0, int64_t b1,
                      int64_t g_offset, const pda_samples_t *out, int nthreads);
 
+/* The same evaluation on the reference's own generators (cuRAND scrambled Sobol64 per thread,
+ * dimension t % 20000 at offset 1234, + its xor128 stream; src/mc.cu:366-455, gen_rand.cuh:7-25):
+ * what the reference's class mc computes on the GPU.  `evals` evaluations on persistent states;
+ * mcE is [evals][N*R].  dirvec/scramble: the 20000 x 64 / 20000 tables of
+ * CURAND_SCRAMBLED_DIRECTION_VECTORS_64_JOEKUO6 from libcurand's host API. */
+void pda_oracle_eval_sobol(const pda_bursts_t *bursts, const pda_params_t *prm, int R, int64_t N,
+                           const uint64_t *dirvec20000x64, const uint64_t *scramble20000,
+                           int evals, float *mcE, int nthreads);
+
 /* boost::histogram regular axis [0,1) with nb bins; hist has nb+2 entries:
  * [0,nb) inner, [nb] overflow (x>=1 or NaN), [nb+1] underflow (x<0). counts are ADDED. */
 void pda_oracle_hist(const float *x, int64_t n, int nb, uint64_t *hist);

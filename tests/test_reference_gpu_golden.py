@@ -44,6 +44,29 @@ def test_host_build_replays_the_reference_gpu_bit_for_bit(ref, path):
     assert not np.array_equal(want[0], want[1])      # the second evaluation continues the sequences
 
 
+@pytest.mark.parametrize("path", GOLD, ids=[os.path.basename(p)[:-4] for p in GOLD])
+def test_c_restatement_replays_the_reference_gpu_bit_for_bit(oracle, path):
+    """The oracle itself (oracle/pda_oracle.c, no reference source involved) on the reference's
+    generators: equal to the reference's GPU run, so the checker is pinned on any box."""
+    d = np.load(path)
+    cfg, nb, R = int(d["cfg"]), int(d["n_bursts"]), int(d["R"])
+    w = synth.workload(cfg, n_bursts=nb, R=R)
+    want = d["mcE"]
+    got = oracle.eval_sobol(w.bursts(), w.n_states, w.args[0], R, evals=want.shape[0])
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), f"{(got != want).mean():.4%} differ"
+
+
+@pytest.mark.parametrize("cfg", [1, 2, 3, 5])
+def test_c_restatement_equals_host_build_on_sobol(oracle, ref, cfg):
+    w = synth.workload(cfg, n_bursts=6000, R=8)      # 48 000 threads: beyond the 20 000 dimensions
+    b = w.bursts()
+    a = oracle.eval_sobol(b, w.n_states, w.args[0], 8, evals=3)
+    r = ref.mc_kernel_sobol(b, w.n_states, w.args[0], 8, evals=3)
+    assert np.array_equal(a.view(np.uint32), r.view(np.uint32))
+    h = oracle.eval_sobol(b, w.n_states, w.args[0], 8, evals=1, N=2500)   # N only sets the thread count (Q7)
+    assert np.array_equal(h, ref.mc_kernel_sobol(b, w.n_states, w.args[0], 8, evals=1, N=2500))
+
+
 def test_sobol_tables_are_curands():
     """First words of dimension 0/1 after curand_init(..., offset 1234), read off a B200
     (tools/sobol_probe.cu)."""
