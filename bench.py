@@ -272,6 +272,12 @@ def main():
         run_reference(args, w, rank)
         return
 
+    # stdout carries exactly ONE line, the JSON: anything a library prints there meanwhile (NCCL's
+    # version banner, for one) is sent to stderr by pointing fd 1 at fd 2 until the line is written
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
     import torch
     import torch.distributed as dist
     from gsmfretda_b200 import capi
@@ -469,7 +475,8 @@ def main():
         if not args.no_cpu and world == 1:
             torch.cuda.synchronize()
             out["cpu_baseline"]["reference_on_gpu"] = reference_on_gpu(args.cfg, min(B, 100000))
-        print(json.dumps(out), flush=True)
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(out) + "\n").encode())
     if mc is not None:
         mc.close()
     if world > 1:
