@@ -18,6 +18,7 @@ GSM_KEEP_MCE = 1
 GSM_KEEP_COUNTS = 2
 GSM_FORCE_RAW64 = 4
 GSM_NO_INDEX = 8
+GSM_NO_TIMING = 16
 GSM_MODE_REPLAY = 0
 GSM_MODE_NORMAL = 1
 GSM_MODE_REFERENCE = 2

@@ -782,7 +782,8 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
         }
         a.sob_dv = c->d_sob_dv; a.sob_state = s.d_sob_state; a.xs_state = s.d_xs_state;
     }
-    CK(cudaEventRecord(s.ev0, s.stream));
+    const bool timing = !(c->flags & GSM_NO_TIMING);
+    if (timing) CK(cudaEventRecord(s.ev0, s.stream));
     if (s.P == 1 && !c->comm) {
         // one vector: it rides in the launch parameters (run_resident re-sends the same bytes)
         a.use_inl = 1;
@@ -807,7 +808,7 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
         if (a.sum_ai) CK(cudaMemcpyAsync(s.h_cnt, s.d_cnt, samples * sizeof(long long), cudaMemcpyDeviceToHost, s.stream));
         if (a.n_steps) CK(cudaMemcpyAsync(s.h_steps, s.d_steps, samples * sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
     }
-    CK(cudaEventRecord(s.ev1, s.stream));
+    if (timing) CK(cudaEventRecord(s.ev1, s.stream));
     s.res_P = s.P; s.res_nbp = nbp;
     s.epoch += (uint32_t)s.P;
     s.ran = true;
@@ -907,7 +908,7 @@ uint64_t gsm_result_flags(const gsm_ctx* c, int sid)
 }
 float gsm_last_elapsed_ms(gsm_ctx* c, int sid)
 {
-    if (!c || sid < 0 || sid >= (int)c->slots.size() || !c->slots[sid].ran) return -1.0f;
+    if (!c || sid < 0 || sid >= (int)c->slots.size() || !c->slots[sid].ran || (c->flags & GSM_NO_TIMING)) return -1.0f;
     float ms = -1.0f;
     if (cudaEventElapsedTime(&ms, c->slots[sid].ev0, c->slots[sid].ev1) != cudaSuccess) { cudaGetLastError(); return -1.0f; }
     return ms;

@@ -44,6 +44,7 @@ class mc {
     struct Options {
         bool keep_mce = true;      // fill hmcE[sid] like the reference (costs an N*R-float copy per run)
         bool force_raw64 = false;  // keep the reference's 16 B/photon layout
+        bool timing = false;       // bracket every run with CUDA events (gsm_last_elapsed_ms); the reference has none
         uint32_t seed = 0x9E3779B9u;
         int fret_hist_num = 200;   // cmdline.ggo:14
         int left_pad = 2;          // main.cpp:155
@@ -67,7 +68,8 @@ class mc {
           streamNum(0), streams(nullptr)
     {
         gpuuuid[0] = 0;
-        unsigned flags = (opt.keep_mce ? GSM_KEEP_MCE : 0u) | (opt.force_raw64 ? GSM_FORCE_RAW64 : 0u);
+        unsigned flags = (opt.keep_mce ? GSM_KEEP_MCE : 0u) | (opt.force_raw64 ? GSM_FORCE_RAW64 : 0u) |
+                         (opt.timing ? 0u : GSM_NO_TIMING);
         int rc = gsm_create(id, _streamNum, flags, &ctx);
         if (rc == GSM_EINVAL) {  // "gpu id set error!" (mc.cu:228-231): the reference returns quietly
             std::printf("gpu id set error!\n");

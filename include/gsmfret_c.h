@@ -46,6 +46,8 @@ extern "C" {
 #define GSM_KEEP_COUNTS 2u  /* also return per-sample integer acceptor counts and dwell steps */
 #define GSM_FORCE_RAW64 4u  /* do not pack photons: read burst_ad/burst_dd as uploaded */
 #define GSM_NO_INDEX 8u     /* packed photons without the window index: photon-by-photon scan */
+#define GSM_NO_TIMING 16u   /* do not bracket every run with CUDA events (gsm_last_elapsed_ms returns -1):
+                               two driver calls less per evaluation, for nodes that evaluate small bursts sets */
 
 typedef struct gsm_ctx gsm_ctx;
 
