@@ -141,7 +141,11 @@ class CpuPath:
         import oracle_py
         self.w = w
         self.O = oracle_py.Oracle()
-        self.cores = self.O.num_threads()
+        # every host core this process may run on, whatever OMP_NUM_THREADS says (torchrun sets it to 1)
+        try:
+            self.cores = len(os.sched_getaffinity(0))
+        except AttributeError:
+            self.cores = os.cpu_count() or self.O.num_threads()
         self.use_ref = oracle_py.have_ref()
         self.R = R
         self.note = ""
@@ -161,11 +165,12 @@ class CpuPath:
         w, O = self.w, self.O
         t0 = time.perf_counter()
         if self.use_ref:
-            e = self.Rf.mc_kernel(self.b, w.n_states, w.args[0], self.R, SEED & 0xFFFFFFFF, 1, N=nb_)
+            e = self.Rf.mc_kernel(self.b, w.n_states, w.args[0], self.R, SEED & 0xFFFFFFFF, 1, N=nb_, nthreads=self.cores)
             h = O.hist(e, NB)                     # streamWorker's host histogram + chi-square
             O.chi2(self.ohist, h, NB, self.R, LEFT_PAD, w.n_states)
         else:
-            O.eval_chi2(self.b, w.n_states, w.args[0], self.R, SEED & 0xFFFFFFFF, 1, self.ohist, NB, LEFT_PAD, 0, nb_)
+            O.eval_chi2(self.b, w.n_states, w.args[0], self.R, SEED & 0xFFFFFFFF, 1, self.ohist, NB, LEFT_PAD, 0, nb_,
+                        nthreads=self.cores)
         return time.perf_counter() - t0
 
     def timed(self, seconds_hint):
