@@ -104,3 +104,17 @@ def test_live_against_the_reference_class_on_this_gpu(gsm):
     for ev in range(2):
         differ = int((got[ev][0].view(np.uint32) != want[ev].view(np.uint32)).sum())
         assert differ <= 10, (ev, differ)
+
+
+@pytest.mark.parametrize("layout_kw", [{}, {"no_index": True}, {"force_raw64": True}])
+@pytest.mark.parametrize("name", ["edge_mixed_p0", "edge_far_ticks_p0"])
+def test_edge_bursts_against_the_oracle_on_sobol(gsm, oracle, name, layout_kw):
+    """Empty, zero-duration and one-photon bursts, ticks far from 0, three evaluations: the oracle's
+    Sobol draw source (pinned on the reference's GPU run and on the host build of its sources)."""
+    from helpers import load_golden
+    b, d = load_golden(name)
+    n, R = int(d["n"]), int(d["R"])
+    want = oracle.eval_sobol(b, n, d["args"], R, evals=3)
+    got = evaluations(gsm, b, n, d["args"], R, 3, **layout_kw)
+    for ev in range(3):
+        assert np.array_equal(got[ev][0].view(np.uint32), want[ev].view(np.uint32)), ev

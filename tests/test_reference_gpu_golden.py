@@ -82,3 +82,15 @@ def test_sobol_tables_are_curands():
         return x
     assert first(0) == 0x4d14c2df07cb3028 and first(1) == 0x8e2c652faa03ff04
     assert first(3) == 0x2855b4fb409ff155 and first(12) == 0x73462c7a37d15205
+
+
+@pytest.mark.parametrize("name", ["edge_mixed_p0", "edge_far_ticks_p0"])
+def test_sobol_draw_source_on_edge_bursts(oracle, ref, name):
+    """Empty, zero-duration and one-photon bursts, ticks far from 0: a thread whose burst has no
+    duration still takes the initial-state draw (mc.cu:110 precedes the loop)."""
+    from helpers import load_golden
+    b, d = load_golden(name)
+    n, R = int(d["n"]), int(d["R"])
+    a = oracle.eval_sobol(b, n, d["args"], R, evals=3)
+    r = ref.mc_kernel_sobol(b, n, d["args"], R, evals=3)
+    assert np.array_equal(a.view(np.uint32), r.view(np.uint32))
