@@ -63,3 +63,35 @@ def test_local_node_matches_oracle(oracle, tmp_path):
         assert np.array_equal(hist, oh), (ji, epoch, int(hist.sum()), int(oh.sum()))
         c = oracle.chi2(ohist, oh, NB, 8, LEFT_PAD, n)
         assert abs(chi2 - c) <= 2e-6 * abs(c)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("parts", [1, 2, 5])
+def test_split_node_matches_oracle(oracle, tmp_path, parts):
+    """One dataset cut into `parts` burst ranges, one context each (sharing the GPUs there are),
+    histogram exchange fused into the evaluation kernel, driven from C++: the global histogram and
+    chi-square equal the oracle's over the whole dataset, whatever the number of parts."""
+    build()
+    exe = os.path.join(HOST, "split_node")
+    w = synth.workload(5, n_bursts=1500, R=4)
+    b = w.bursts()
+    synth.save_bin(b, str(tmp_path / "b.bin"))
+    vecs = [(w.n_states, w.args[0]), (2, synth.workload(2).args[0]), (3, synth.workload(3).args[0])]
+    with open(tmp_path / "p.txt", "w") as f:
+        for n, a in vecs:
+            f.write(f"{n} " + " ".join(repr(float(x)) for x in a) + "\n")
+    r = subprocess.run([exe, str(tmp_path / "b.bin"), str(tmp_path / "p.txt"), str(tmp_path / "o.txt"), str(parts), "4", "42"],
+                       capture_output=True, text=True, timeout=180)
+    assert r.returncode == 0, (r.stdout, r.stderr)
+    assert f"split into {parts} parts" in r.stdout
+    rows = [l.split() for l in open(tmp_path / "o.txt") if l.strip()]
+    assert len(rows) == len(vecs)
+    ohist = oracle.observed_hist(b, NB)
+    for row in rows:
+        ji, epoch, chi2 = int(row[0]), int(row[2]), float(row[3])
+        hist = np.array([int(x) for x in row[4:]], np.uint64)
+        n, a = vecs[ji]
+        oh = oracle.hist(oracle.eval(b, n, a, 4, 42, epoch)["mcE"], NB)
+        assert np.array_equal(hist, oh), (ji, int(hist.sum()), int(oh.sum()))
+        c = oracle.chi2(ohist, oh, NB, 4, LEFT_PAD, n)
+        assert abs(chi2 - c) <= 2e-6 * abs(c)
