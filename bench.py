@@ -472,9 +472,11 @@ def main():
             "clocks": clk,
             "chi2": chi2_last,
         }
-        if not args.no_cpu:
+        if not args.no_cpu and world == 1:   # the CPU baseline is reported at N = 1 only
             cb = cpu_leg(w, min(B, 100000), R, seconds_hint=12.0)
             out["cpu_baseline"] = cb
+        else:
+            out["cpu_baseline"] = None
         mc.close()
         mc = None
         if not args.no_cpu and world == 1:
