@@ -3,6 +3,7 @@
 // /root/reference/src/call_main.cpp:195-227).
 //
 //   split_node <bursts.bin> <params.txt> <out.txt> [parts=#GPUs] [reSampleTimes=4] [seed=1]
+//   split_node --plan <bursts.bin> <parts>      print the burst ranges only (no GPU needed)
 //
 // The bursts are cut into `parts` contiguous ranges balanced by photon count (the rule of
 // gsmfretda_b200/sharding.py); part r lives in a context of its own on GPU r % #GPUs with the
@@ -48,8 +49,24 @@ static std::vector<int64_t> split_bursts(const std::vector<int>& ph, int parts)
     return cuts;
 }
 
+static int plan_only(const char* path, int parts)
+{
+    FILE* f = std::fopen(path, "rb");
+    if (!f) { std::perror(path); return 1; }
+    char magic[4]; uint32_t ver; int64_t B, Nph; float hdr[4];
+    if (fread(magic, 1, 4, f) != 4 || std::memcmp(magic, "GSMB", 4) || fread(&ver, 4, 1, f) != 1 || ver != 1 ||
+        fread(&B, 8, 1, f) != 1 || fread(&Nph, 8, 1, f) != 1 || fread(hdr, 4, 4, f) != 4) { std::fprintf(stderr, "bad header\n"); return 1; }
+    std::vector<int> ph;
+    if (std::fseek(f, (long)(3 * B * 8), SEEK_CUR) != 0 || !rd(f, ph, B)) { std::fprintf(stderr, "short file\n"); return 1; }
+    std::fclose(f);
+    const std::vector<int64_t> cuts = split_bursts(ph, parts);
+    for (int r = 0; r < parts; ++r) std::printf("%" PRId64 " %" PRId64 "\n", cuts[r], cuts[r + 1]);
+    return 0;
+}
+
 int main(int argc, char** argv)
 {
+    if (argc == 4 && std::strcmp(argv[1], "--plan") == 0) return plan_only(argv[2], std::atoi(argv[3]));
     if (argc < 4) { std::fprintf(stderr, "usage: %s bursts.bin params.txt out.txt [parts] [R] [seed]\n", argv[0]); return 2; }
     const int ngpu = gsm_device_count();
     if (ngpu < 1) { std::fprintf(stderr, "no sm_100 device: this node has no CPU path\n"); return 1; }

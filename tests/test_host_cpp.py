@@ -65,6 +65,21 @@ def test_local_node_matches_oracle(oracle, tmp_path):
         assert abs(chi2 - c) <= 2e-6 * abs(c)
 
 
+def test_split_node_plans_like_sharding_py(tmp_path):
+    """The C++ burst-range planner of split_node equals gsmfretda_b200.sharding.split_bursts."""
+    from gsmfretda_b200 import sharding
+    build()
+    exe = os.path.join(HOST, "split_node")
+    for cfg, nb in ((2, 3000), (5, 777), (1, 5)):
+        b = synth.workload(cfg, n_bursts=nb).bursts()
+        synth.save_bin(b, str(tmp_path / "b.bin"))
+        for parts in (1, 2, 3, 8):
+            r = subprocess.run([exe, "--plan", str(tmp_path / "b.bin"), str(parts)], capture_output=True, text=True, timeout=60)
+            assert r.returncode == 0, r.stderr
+            got = [tuple(int(x) for x in l.split()) for l in r.stdout.splitlines() if l.strip()]
+            assert got == sharding.split_bursts(b.ph_count, parts), (cfg, nb, parts)
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("parts", [1, 2, 5])
 def test_split_node_matches_oracle(oracle, tmp_path, parts):
