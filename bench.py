@@ -43,6 +43,11 @@ NB, LEFT_PAD = 200, 2
 SEED = 20261104
 # algorithmic thread-instructions per burst-sample, frozen from SURVEY.md §8(d) before optimisation
 ALGO_OPS = {1: 400.0, 2: 610.0, 3: 1230.0, 4: 610.0, 5: 980.0}
+try:   # roofline.json holds the frozen constants; the literals above are the same numbers
+    with open(os.path.join(ROOT, "roofline.json")) as _f:
+        ALGO_OPS = {int(k): float(v) for k, v in json.load(_f)["algorithmic_thread_ops_per_sample"].items()}
+except Exception:   # noqa: BLE001
+    pass
 
 
 def measured_peaks():
