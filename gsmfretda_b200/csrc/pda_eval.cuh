@@ -17,8 +17,14 @@
 namespace pda {
 
 constexpr int kModeReplay = 0, kModeNormal = 1, kModeReference = 2;
-constexpr int kBlock = 256;
-constexpr int kChunkMax = 256;          // most consecutive samples a warp draws per ticket (EvalArgs::chunk)
+#ifndef PDA_BLOCK
+#define PDA_BLOCK 256
+#endif
+#ifndef PDA_CHUNK_MAX
+#define PDA_CHUNK_MAX 256
+#endif
+constexpr int kBlock = PDA_BLOCK;
+constexpr int kChunkMax = PDA_CHUNK_MAX;  // most consecutive samples a warp draws per ticket (EvalArgs::chunk)
 constexpr int kMaxBins = 1024;          // nb + 2 <= kMaxBins
 constexpr uint32_t kStepCap = 1u << 20; // guards the GPU against rates <= 0 (a hang in the reference)
 
@@ -97,7 +103,10 @@ struct Lane {
     // walk state
     Xor128 xs;          // replay mode only
     float F, acc, spent;
-    int64_t bin0;
+    // left edge of the current window as the float the reference converts it to every step
+    // ((float)bin0, mc.cu:132).  After the first window bin0 is itself the truncation of a float
+    // sum, so its float image is known without a 64-bit integer conversion.
+    float fb;
     int first, si;
     uint32_t step;
     // reference-draws mode: position in the thread's Sobol64 sequence
@@ -241,7 +250,7 @@ __device__ __forceinline__ void lane_begin(Lane& L, const SmemParams& sp, const 
         L.xs.seed((uint64_t)sd.x | ((uint64_t)sd.y << 32));
     }
     L.F = 0.0f; L.acc = 0.0f; L.spent = 0.0f;
-    L.bin0 = L.start;
+    L.fb = (float)L.start;
     L.first = 0;
     L.step = 0;
 }
@@ -288,10 +297,17 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
     else tau = det_logf(u01(w.y)) / (-sp.K[sj + si * n]);
     L.spent = L.spent + tau;
     int64_t bin1;
-    if (L.spent >= L.T)
-        bin1 = __ldg(&a.bursts[a.b0 + L.bl].stop);
-    else
-        bin1 = (int64_t)((float)L.bin0 + (kFast ? __fdividef(L.spent, a.clk_p) : L.spent / a.clk_p));
+    // bg: the left edge as an integer again (exact: fb holds (float)bin0, and past the first
+    // window bin0 is the truncation of that very float)
+    const int64_t bin0 = kBg ? (L.step == 0 ? L.start : (int64_t)L.fb) : 0;
+    if (L.spent >= L.T) {
+        bin1 = __ldg(&a.bursts[a.b0 + L.bl].stop);   // last window of the sample: fb is not read again
+    } else {
+        const float f = L.fb + (kFast ? __fdividef(L.spent, a.clk_p) : L.spent / a.clk_p);
+        bin1 = (int64_t)f;
+        // (float)bin1: truncation toward zero is exact in float while the conversion does not saturate
+        L.fb = fabsf(f) < 9.0e18f ? truncf(f) : (float)bin1;
+    }
 
     Window win;
     if (kLayout == 0) {
@@ -315,7 +331,7 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
         if (!kBg) {
             f_i = floorf(f_if + 0.5f);
         } else if (kFast) {
-            const float t_diff = (float)(bin1 - L.bin0) * a.clk_p;
+            const float t_diff = (float)(bin1 - bin0) * a.clk_p;
             const float rf_ia = (1.0f - kDexDirAem) * (float)win.f_ia;
             const float rf_id = (kGamma - kDch2Ach) * (float)win.f_id;
             // one Philox block serves both channels: x/y acceptor (Poisson word, fall-back
@@ -329,7 +345,7 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
         } else if (kSobol) {
             // draw_P_B_Tr (gen_rand.cuh:92-107): one 64-bit word per Poisson draw, a further
             // word only when the draw exceeds the photons there are
-            const float t_diff = (float)(bin1 - L.bin0) * a.clk_p;
+            const float t_diff = (float)(bin1 - bin0) * a.clk_p;
             const float rf_ia = (1.0f - kDexDirAem) * (float)win.f_ia;
             unsigned long long x = sobol_next(L);
             uint32_t sv = poisson_itr((uint32_t)(x >> 32), (uint32_t)x, (double)(t_diff * a.bg_ad_rate));
@@ -342,7 +358,7 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
                                                              : floorf(rf_id * u01((uint32_t)(sobol_next(L) >> 32)));
             f_i = floorf(f_if - bg_d - bg_a + 0.5f);
         } else {
-            const float t_diff = (float)(bin1 - L.bin0) * a.clk_p;
+            const float t_diff = (float)(bin1 - bin0) * a.clk_p;
             const float rf_ia = (1.0f - kDexDirAem) * (float)win.f_ia;
             const u32x4 ba = philox4x32_10(g, L.rep, L.step, kSlotBgA, a.seed, epoch);
             uint32_t sv = poisson_itr(ba.x, ba.y, (double)(t_diff * a.bg_ad_rate));
@@ -367,7 +383,6 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
         }
     }
     L.acc += (float)ai;
-    L.bin0 = bin1;
     L.si = sj;
     L.step++;
 }

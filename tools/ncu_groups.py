@@ -1,38 +1,60 @@
 #!/usr/bin/env python
-"""Group the per-line table of tools/ncu_lines.py by phase of the evaluation kernel.
+"""Group the per-line table of tools/ncu_lines.py by the function the line sits in (function
+ranges are found in the current sources: a definition starts at a line containing `name(` at brace
+depth 0 of the namespace and ends where its braces close).
 usage: python tools/ncu_groups.py lines_all.txt"""
-import re, sys
-groups = [
- ("philox", "pda_device.cuh", 25, 55), ("u01", "pda_device.cuh", 56, 60),
- ("det_logf", "pda_device.cuh", 61, 84), ("det_log f64", "pda_device.cuh", 85, 108), ("det_exp f64", "pda_device.cuh", 109, 130),
- ("det_norm_icdf", "pda_device.cuh", 131, 164), ("pow6/root6", "pda_device.cuh", 165, 182),
- ("xor128", "pda_device.cuh", 183, 209), ("binomial_inversion f64", "pda_device.cuh", 210, 235),
- ("btpe", "pda_device.cuh", 236, 316), ("binomial dispatch", "pda_device.cuh", 317, 335),
- ("poisson_itr", "pda_device.cuh", 355, 378),
- ("icdf_fast", "pda_device.cuh", 379, 417), ("binomial_fast", "pda_device.cuh", 418, 453),
- ("poisson_fast", "pda_device.cuh", 454, 470), ("cell_of", "pda_device.cuh", 471, 480), ("hist_index", "pda_device.cuh", 481, 493),
- ("pick", "pda_eval.cuh", 64, 76), ("lane_g/off", "pda_eval.cuh", 100, 112),
- ("scan_linear", "pda_eval.cuh", 128, 158), ("scan_indexed", "pda_eval.cuh", 159, 193),
- ("lane_begin", "pda_eval.cuh", 194, 221), ("lane_step", "pda_eval.cuh", 222, 311),
- ("kernel prologue", "pda_eval.cuh", 355, 403), ("refill", "pda_eval.cuh", 404, 499),
- ("step+finish", "pda_eval.cuh", 500, 528), ("epilogue", "pda_eval.cuh", 529, 556),
-]
+import os, re, sys
+
+SRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "gsmfretda_b200", "csrc")
+
+
+def function_ranges(path):
+    out = []
+    depth = 0
+    cur = None
+    pending = None
+    for no, line in enumerate(open(path), 1):
+        code = line.split("//")[0]
+        if depth <= 1 and cur is None:
+            m = re.search(r"\b([A-Za-z_]\w*)\s*\(", code)
+            if m and not code.lstrip().startswith(("#", "}", "if", "for", "while", "return", "static_assert")):
+                pending = (m.group(1), no)
+        opens, closes = code.count("{"), code.count("}")
+        if pending and opens and cur is None:
+            cur = (pending[0], pending[1], depth)
+            pending = None
+        depth += opens - closes
+        if cur and depth <= cur[2]:
+            out.append((cur[0], cur[1], no))
+            cur = None
+    return out
+
+
+ranges = {}
+for f in os.listdir(SRC):
+    if f.endswith((".cuh", ".cu", ".h")):
+        ranges[f] = function_ranges(os.path.join(SRC, f))
+
 tot = {}
-for l in open(sys.argv[1]).read().split('\n')[2:]:
-    m = re.match(r'(\S.*?)\s+([\d.]+)\s+([\d.]+)\s+([\d.]+)\s+(\d+)', l)
-    if not m: continue
+for l in open(sys.argv[1]).read().split("\n")[2:]:
+    m = re.match(r"(\S.*?)\s+([\d.]+)\s+([\d.]+)\s+([\d.]+)\s+(\d+)", l)
+    if not m:
+        continue
     key, wi, ss, act = m.group(1), float(m.group(2)), float(m.group(3)), float(m.group(4))
-    g = None
-    mm = re.match(r'(\S+):(\d+)$', key)
+    g = key
+    mm = re.match(r"(\S+):(\d+)$", key)
     if mm:
         f, n = mm.group(1), int(mm.group(2))
-        for name, ff, a, b in groups:
-            if f == ff and a <= n <= b: g = name; break
-        if g is None: g = f
-    else: g = key
+        g = f
+        for name, a, b in ranges.get(f, []):
+            if a <= n <= b:
+                g = f"{f}:{name}"
     t = tot.setdefault(g, [0, 0, 0])
-    t[0] += wi; t[1] += ss; t[2] += wi * act
+    t[0] += wi
+    t[1] += ss
+    t[2] += wi * act
 print(open(sys.argv[1]).readline().strip())
 for g, t in sorted(tot.items(), key=lambda kv: -kv[1][0]):
-    if t[0] < 0.005 and t[1] < 0.05: continue
-    print(f"{g:58s} warp-inst {t[0]:6.2f}%  samples {t[1]:6.2f}%  act {t[2]/max(t[0],1e-9):5.1f}")
+    if t[0] < 0.05 and t[1] < 0.05:
+        continue
+    print(f"{g:50s} warp-inst {t[0]:6.2f}%  samples {t[1]:6.2f}%  act {t[2]/max(t[0],1e-9):5.1f}")
