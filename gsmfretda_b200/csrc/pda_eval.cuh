@@ -233,7 +233,6 @@ __device__ __forceinline__ void lane_begin(Lane& L, const SmemParams& sp, const 
     L.off4 = (uint32_t)r1.z;      // packed layouts; the raw layout re-reads its 64-bit offset
     L.scale = (uint32_t)r1.w;
     L.si = 0;
-    constexpr bool kFast = kMode == kModeNormal;
     if (kMode == kModeReference) {
         // the reference's thread tidx = burst * R + repeat resumes its Sobol sequence and its
         // xor128 stream where the previous evaluation left them (mc.cu:366-455, quirk Q8)
@@ -243,12 +242,8 @@ __device__ __forceinline__ void lane_begin(Lane& L, const SmemParams& sp, const 
         L.sob_dv = a.sob_dv + 64u * (unsigned)(t % 20000u);
         const uint4 xs = a.xs_state[t];
         L.xs.s0 = xs.x; L.xs.s1 = xs.y; L.xs.s2 = xs.z; L.xs.s3 = xs.w;
-    } else if (!kFast) {
-        // replay mode: the binomial stream of the sample (draw contract); the
-        // normal mode needs no per-sample block, its draws all come from the step blocks
-        const u32x4 sd = philox4x32_10(lane_g(a, L), rep, 0u, kSlotSeed, a.seed, epoch);
-        L.xs.seed((uint64_t)sd.x | ((uint64_t)sd.y << 32));
     }
+    // replay mode: the xor128 stream of the sample is seeded from its step-0 block (lane_step)
     L.F = 0.0f; L.acc = 0.0f; L.spent = 0.0f;
     L.fb = (float)L.start;
     L.first = 0;
@@ -265,7 +260,8 @@ __device__ __forceinline__ void lane_save_reference(const Lane& L, const EvalArg
 
 // one dwell window (one trip of the reference's while loop, mc.cu:117-191)
 template <int kLayout, bool kBg, int kMode>
-__device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const EvalArgs& a, uint32_t epoch)
+__device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const EvalArgs& a, uint32_t epoch,
+                                          const double2* __restrict__ ltab)
 {
     constexpr bool kFast = kMode == kModeNormal;
     constexpr bool kSobol = kMode == kModeReference;
@@ -283,10 +279,17 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
         w = philox4x32_10(g, L.rep, L.step, kSlotStep, a.seed, epoch);
     }
     if (L.step == 0) {
-        // initial state (mc.cu:110).  Replay: word 3 of the step-0 block (draw contract).  Normal:
-        // the low bytes of the four words — the uniforms of this block are built from the top 24
-        // bits of each word, so those 32 bits are an independent word that costs no Philox call
-        const uint32_t iw = kFast ? ((w.x & 0xffu) | ((w.y & 0xffu) << 8) | ((w.z & 0xffu) << 16) | (w.w << 24)) : w.w;
+        // initial state (mc.cu:110).  Counter modes: the low bytes of the words — the uniforms of
+        // this block are built from the top 24 bits of each word, so those bits are an independent
+        // word that costs no Philox call.  Replay: word 3 seeds the sample's xor128 stream (the
+        // role of setup_kernel's rk_seed(curand()), gen_rand.cuh:19-21); normal mode spends it on
+        // the binomial and takes a fourth low byte from it.
+        uint32_t iw = w.w;
+        if (kFast) iw = (w.x & 0xffu) | ((w.y & 0xffu) << 8) | ((w.z & 0xffu) << 16) | (w.w << 24);
+        else if (!kSobol) {
+            iw = ((w.x & 0xffu) << 24) | ((w.y & 0xffu) << 16) | ((w.z & 0xffu) << 8) | 0x80u;
+            L.xs.seed((uint64_t)w.w);
+        }
         L.si = pick(sp.cumP, n, u01(iw));
     }
     const int si = L.si;
@@ -336,7 +339,7 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
             const float rf_id = (kGamma - kDch2Ach) * (float)win.f_id;
             // one Philox block serves both channels: x/y acceptor (Poisson word, fall-back
             // uniform), z/w donor
-            const u32x4 bw = philox4x32_10(g, L.rep, L.step, kSlotBgA, a.seed, epoch);
+            const u32x4 bw = philox4x32_10(g, L.rep, L.step, kSlotBg, a.seed, epoch);
             float sv = (float)poisson_fast(bw.x, t_diff * a.bg_ad_rate);
             const float bg_a = (sv <= rf_ia) ? sv : floorf(rf_ia * u01(bw.y));
             sv = (float)poisson_fast(bw.z, t_diff * a.bg_dd_rate);
@@ -360,13 +363,14 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
         } else {
             const float t_diff = (float)(bin1 - bin0) * a.clk_p;
             const float rf_ia = (1.0f - kDexDirAem) * (float)win.f_ia;
-            const u32x4 ba = philox4x32_10(g, L.rep, L.step, kSlotBgA, a.seed, epoch);
-            uint32_t sv = poisson_itr(ba.x, ba.y, (double)(t_diff * a.bg_ad_rate));
-            const float bg_a = ((float)(int32_t)sv <= rf_ia) ? (float)(int32_t)sv : floorf(rf_ia * u01(ba.z));
+            // one block for both channels: x / z the high word of each Poisson draw (low word 0),
+            // y / w the fall-back uniforms
+            const u32x4 bw = philox4x32_10(g, L.rep, L.step, kSlotBg, a.seed, epoch);
+            uint32_t sv = poisson_itr(bw.x, 0u, (double)(t_diff * a.bg_ad_rate));
+            const float bg_a = ((float)(int32_t)sv <= rf_ia) ? (float)(int32_t)sv : floorf(rf_ia * u01(bw.y));
             const float rf_id = (kGamma - kDch2Ach) * (float)win.f_id;
-            const u32x4 bq = philox4x32_10(g, L.rep, L.step, kSlotBgD, a.seed, epoch);
-            sv = poisson_itr(bq.x, bq.y, (double)(t_diff * a.bg_dd_rate));
-            const float bg_d = ((float)(int32_t)sv <= rf_id) ? (float)(int32_t)sv : floorf(rf_id * u01(bq.z));
+            sv = poisson_itr(bw.z, 0u, (double)(t_diff * a.bg_dd_rate));
+            const float bg_d = ((float)(int32_t)sv <= rf_id) ? (float)(int32_t)sv : floorf(rf_id * u01(bw.w));
             f_i = floorf(f_if - bg_d - bg_a + 0.5f);
         }
         if (kFast) {
@@ -379,7 +383,7 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
             if (kSobol) w.z = (uint32_t)(sobol_next(L) >> 32);
             const float rd = det_norm_icdf(w.z) * sp.v[si] + sp.rootE[si];
             const float de = 1.0f / (1.0f + det_pow6f(rd / kR0));
-            ai = (int)binomial(L.xs, (int)f_i, (double)de);
+            ai = (int)binomial(L.xs, (int)f_i, (double)de, ltab);
         }
     }
     L.acc += (float)ai;
@@ -562,6 +566,13 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
     extern __shared__ __align__(16) unsigned int s_hist_all[];  // [kWarps][nbp]; the last block reuses it for chi2 terms
     __shared__ int s_last;
     __shared__ WarpCtl s_ctl[kWarps];
+    // the {c_j, L_j} table of det_log (FP64 binomial): divergent lookups are bank conflicts here
+    // instead of L1 sectors
+    __shared__ double2 s_logtab[kMode == kModeNormal ? 1 : 128];
+    if (kMode != kModeNormal) {
+        for (int i = threadIdx.x; i < 128; i += kBlock) s_logtab[i] = kLogTab[i];
+        __syncthreads();
+    }
 
     const int lane = threadIdx.x & 31;
     const int wid = threadIdx.x >> 5;
@@ -696,7 +707,7 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
 
         // ---- one dwell window for every active lane -------------------------------------
         if (active) {
-            lane_step<kLayout, kBg, kMode>(L, sp, a, wc.epoch);
+            lane_step<kLayout, kBg, kMode>(L, sp, a, wc.epoch, s_logtab);
             bool fin = !(L.T > L.spent);
             if (!fin && L.step >= kStepCap) {
                 atomicOr(a.counters + 2, 1ull);

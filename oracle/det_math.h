@@ -13,8 +13,9 @@
  *                                 /usr/local/cuda/include/curand_normal.h:240-257)
  *   det_log/det_exp <- log/exp   in rk_binomial_*      (/root/reference/src/binom.cuh:81,86,109,120-122,145)
  *                      exp       in cuRAND's Poisson   (curand_poisson.h:436-463)
- * The algorithms are the classic Sun fdlibm argument reductions (log, logf, exp)
- * and M. Giles' single-precision erfinv polynomial ("Approximating the erfinv
+ * The algorithms: polynomial logf on [2/3, 4/3); table-driven log (Tang's reduction with
+ * Gal's accurate table); Taylor exp after a two-step Cody-Waite reduction; and M. Giles'
+ * single-precision erfinv polynomial ("Approximating the erfinv
  * function", GPU Computing Gems 2011).
  */
 #ifndef ORACLE_DET_MATH_H
@@ -28,83 +29,94 @@ static inline float om_u2f(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
 static inline uint64_t om_d2u(double f) { uint64_t u; memcpy(&u, &f, 8); return u; }
 static inline double om_u2d(uint64_t u) { double f; memcpy(&f, &u, 8); return f; }
 
-/* natural log of a positive, normal, finite float. */
+/* ---- draw contract v2: division-free, fma-based, table-driven -------------------------
+ * The three functions below are DEFINITIONS (the contract's logf / log / exp), chosen so that
+ * the sm_100a kernel evaluates them in a handful of fused multiply-adds: no division, no
+ * hardware approximation (MUFU) whose bits a CPU could not restate.  Each operation is one
+ * IEEE-754 rounding: +, *, fma.  Measured against extended precision
+ * (tests/test_oracle_primitives.py): logf <= 0.94 ulp, log <= 0.80 ulp, exp <= 1.02 ulp.
+ * Constants: oracle/det_tables.h (tools/gen_det_tables.py). */
+#include "det_tables.h"
+
+/* natural log of a positive, normal, finite float:
+ * x = 2^e m, m in [2/3, 4/3); log1p(f) = f - f^2/2 + f^3 Q(f), f = m - 1 */
 static inline float det_logf(float x)
 {
-    const float ln2_hi = 6.9313812256e-01f; /* 0x3f317180 */
-    const float ln2_lo = 9.0580006145e-06f; /* 0x3717f7d1 */
-    const float Lg1 = 0.66666662693f;       /* 0xaaaaaa.0p-24 */
-    const float Lg2 = 0.40000972152f;       /* 0xccce13.0p-25 */
-    const float Lg3 = 0.28498786688f;       /* 0x91e9ee.0p-25 */
-    const float Lg4 = 0.24279078841f;       /* 0xf89e26.0p-26 */
     uint32_t ix = om_f2u(x);
-    ix += 0x3f800000u - 0x3f3504f3u;
-    int k = (int)(ix >> 23) - 0x7f;
-    ix = (ix & 0x007fffffu) + 0x3f3504f3u;
-    float m = om_u2f(ix);
+    uint32_t e = (ix - 0x3f2aaaabu) & 0xff800000u;
+    float m = om_u2f(ix - e);
+    float fi = (float)((int32_t)e >> 23);
     float f = m - 1.0f;
-    float s = f / (2.0f + f);
-    float z = s * s;
-    float w = z * z;
-    float t1 = w * (Lg2 + w * Lg4);
-    float t2 = z * (Lg1 + w * Lg3);
-    float R = t2 + t1;
-    float hfsq = 0.5f * f * f;
-    float dk = (float)k;
-    return dk * ln2_hi - ((hfsq - (s * (hfsq + R) + dk * ln2_lo)) - f);
+    float q = PDA_LOGF_Q7;
+    q = fmaf(q, f, PDA_LOGF_Q6);
+    q = fmaf(q, f, PDA_LOGF_Q5);
+    q = fmaf(q, f, PDA_LOGF_Q4);
+    q = fmaf(q, f, PDA_LOGF_Q3);
+    q = fmaf(q, f, PDA_LOGF_Q2);
+    q = fmaf(q, f, PDA_LOGF_Q1);
+    q = fmaf(q, f, PDA_LOGF_Q0);
+    float r = fmaf(q, f, -0.5f);
+    r = r * f;
+    r = fmaf(r, f, f);
+    return fmaf(fi, 0.693147182f, r);
 }
 
-/* natural log of a positive, normal, finite double. */
+static const double det_log_table[128][2] = PDA_LOG_TABLE_INIT;
+
+/* natural log of a positive, normal, finite double:
+ * x = 2^e m, m in [1, 2), j = top 7 mantissa bits, r = fma(m, c_j, -1), |r| < 2^-7,
+ * log x = (e + [j >= KSPLIT]) ln2 + L_j + log1p(r), log1p by its Taylor series to r^8 */
 static inline double det_log(double x)
+{
+    const double ln2_hi = 6.93147180369123816490e-01; /* 0x3fe62e42fee00000 */
+    const double ln2_lo = 1.90821492927058770002e-10; /* 0x3dea39ef35793c76 */
+    uint64_t ux = om_d2u(x);
+    uint32_t hx = (uint32_t)(ux >> 32);
+    int j = (int)((hx >> 13) & 0x7fu);
+    int kk = (int)(hx >> 20) - 1023 + (j >= PDA_LOG_KSPLIT ? 1 : 0);
+    double m = om_u2d((ux & 0x000fffffffffffffull) | 0x3ff0000000000000ull);
+    double r = fma(m, det_log_table[j][0], -1.0);
+    double q = -0.125;
+    q = fma(q, r, 1.0 / 7.0);
+    q = fma(q, r, -1.0 / 6.0);
+    q = fma(q, r, 0.2);
+    q = fma(q, r, -0.25);
+    q = fma(q, r, 1.0 / 3.0);
+    double s = fma(q, r, -0.5);
+    s = s * (r * r);
+    double dk = (double)kk;
+    double lo = fma(dk, ln2_lo, s);
+    double t = det_log_table[j][1] + (r + lo);
+    return fma(dk, ln2_hi, t);   /* dk ln2_hi is exact (33-bit ln2_hi): one rounding for the large terms */
+}
+
+/* exp of a finite double in [-700, 700]: k = nearest integer to x / ln2 (magic-number
+ * rounding), r = x - k ln2 in two fused steps, Taylor series to r^13, exponent add */
+static inline double det_exp(double x)
 {
     const double ln2_hi = 6.93147180369123816490e-01;
     const double ln2_lo = 1.90821492927058770002e-10;
-    const double Lg1 = 6.666666666666735130e-01;
-    const double Lg2 = 3.999999999940941908e-01;
-    const double Lg3 = 2.857142874366239149e-01;
-    const double Lg4 = 2.222219843214978396e-01;
-    const double Lg5 = 1.818357216161805012e-01;
-    const double Lg6 = 1.531383769920937332e-01;
-    const double Lg7 = 1.479819860511658591e-01;
-    uint64_t ux = om_d2u(x);
-    uint32_t hx = (uint32_t)(ux >> 32);
-    hx += 0x3ff00000u - 0x3fe6a09eu;
-    int k = (int)(hx >> 20) - 0x3ff;
-    hx = (hx & 0x000fffffu) + 0x3fe6a09eu;
-    ux = ((uint64_t)hx << 32) | (ux & 0xffffffffull);
-    double m = om_u2d(ux);
-    double f = m - 1.0;
-    double hfsq = 0.5 * f * f;
-    double s = f / (2.0 + f);
-    double z = s * s;
-    double w = z * z;
-    double t1 = w * (Lg2 + w * (Lg4 + w * Lg6));
-    double t2 = z * (Lg1 + w * (Lg3 + w * (Lg5 + w * Lg7)));
-    double R = t2 + t1;
-    double dk = (double)k;
-    return s * (hfsq + R) + dk * ln2_lo - hfsq + f + dk * ln2_hi;
-}
-
-/* exp of a finite double in [-700, 700]. */
-static inline double det_exp(double x)
-{
-    const double ln2HI = 6.93147180369123816490e-01;
-    const double ln2LO = 1.90821492927058770002e-10;
     const double invln2 = 1.44269504088896338700e+00;
-    const double P1 = 1.66666666666666019037e-01;
-    const double P2 = -2.77777777770155933842e-03;
-    const double P3 = 6.61375632143793436117e-05;
-    const double P4 = -1.65339022054652515390e-06;
-    const double P5 = 4.13813679705723846039e-08;
-    double half = x < 0.0 ? -0.5 : 0.5;
-    int k = (int)(invln2 * x + half); /* truncation toward zero */
-    double dk = (double)k;
-    double hi = x - dk * ln2HI;
-    double lo = dk * ln2LO;
-    double r = hi - lo;
-    double rr = r * r;
-    double c = r - rr * (P1 + rr * (P2 + rr * (P3 + rr * (P4 + rr * P5))));
-    double y = 1.0 + (r * c / (2.0 - c) - lo + hi);
+    const double magic = 6755399441055744.0; /* 1.5 * 2^52 */
+    double t = fma(x, invln2, magic);
+    int32_t k = (int32_t)(uint32_t)om_d2u(t);
+    double dk = t - magic;
+    double r = fma(dk, -ln2_hi, x);
+    r = fma(dk, -ln2_lo, r);
+    double q = 1.0 / 6227020800.0;      /* 1/13! */
+    q = fma(q, r, 1.0 / 479001600.0);   /* 1/12! */
+    q = fma(q, r, 1.0 / 39916800.0);
+    q = fma(q, r, 1.0 / 3628800.0);
+    q = fma(q, r, 1.0 / 362880.0);
+    q = fma(q, r, 1.0 / 40320.0);
+    q = fma(q, r, 1.0 / 5040.0);
+    q = fma(q, r, 1.0 / 720.0);
+    q = fma(q, r, 1.0 / 120.0);
+    q = fma(q, r, 1.0 / 24.0);
+    q = fma(q, r, 1.0 / 6.0);
+    q = fma(q, r, 0.5);
+    double s = fma(q * r, r, r);
+    double y = 1.0 + s;
     /* scale by 2^k, k in [-1010, 1010] so a single exponent add is exact */
     uint64_t uy = om_d2u(y);
     uy += (uint64_t)((int64_t)k << 52);

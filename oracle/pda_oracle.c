@@ -348,9 +348,9 @@ static void eval_sample(const pda_bursts_t *bd, const pda_params_t *prm, int64_t
         memcpy(xs, S->xs, sizeof(xs));
         w.v[3] = (uint32_t)(sobol_next(S) >> 32); /* drawDisIdx before the loop, mc.cu:110 */
     } else {
-        philox4_t sd = philox4x32_10(g, rep, 0u, PDA_SLOT_SEED, seed, epoch);
-        rk_seed((uint64_t)sd.v[0] | ((uint64_t)sd.v[1] << 32), xs);
         w = philox4x32_10(g, rep, 0u, PDA_SLOT_STEP, seed, epoch);
+        rk_seed((uint64_t)w.v[3], xs);
+        w.v[3] = pda_init_word(&w);
     }
 
     float F = 0.0f, acc = 0.0f, spent = 0.0f;
@@ -390,20 +390,22 @@ static void eval_sample(const pda_bursts_t *bd, const pda_params_t *prm, int64_t
                     float rf_ia = (1.0f - PDA_DEXDIRAEM) * (float)f_ia;
                     /* draw_P_B_Tr: one word per Poisson draw, a fall-back uniform only when the
                      * draw exceeds the photons there are (gen_rand.cuh:92-107) */
-                    philox4_t ba = {{0u, 0u, 0u, 0u}}, bq = {{0u, 0u, 0u, 0u}};
-                    if (S) { uint64_t x = sobol_next(S); ba.v[0] = (uint32_t)(x >> 32); ba.v[1] = (uint32_t)x; }
-                    else ba = philox4x32_10(g, rep, step, PDA_SLOT_BG_A, seed, epoch);
-                    uint32_t sv = poisson_itr(ba.v[0], ba.v[1], (double)(t_diff * bd->bg_ad_rate));
+                    /* contract draws: one block for both channels, (Poisson word, fallback) each */
+                    philox4_t bw = {{0u, 0u, 0u, 0u}};
+                    uint32_t p_hi, p_lo = 0u;
+                    if (S) { uint64_t x = sobol_next(S); p_hi = (uint32_t)(x >> 32); p_lo = (uint32_t)x; }
+                    else { bw = philox4x32_10(g, rep, step, PDA_SLOT_BG, seed, epoch); p_hi = bw.v[0]; }
+                    uint32_t sv = poisson_itr(p_hi, p_lo, (double)(t_diff * bd->bg_ad_rate));
                     float bg_a;
                     if ((float)(int32_t)sv <= rf_ia) bg_a = (float)(int32_t)sv;
-                    else bg_a = floorf(rf_ia * u01(S ? (uint32_t)(sobol_next(S) >> 32) : ba.v[2]));
+                    else bg_a = floorf(rf_ia * u01(S ? (uint32_t)(sobol_next(S) >> 32) : bw.v[1]));
                     float rf_id = (PDA_GAMMA - PDA_DCH2ACH) * (float)f_id;
-                    if (S) { uint64_t x = sobol_next(S); bq.v[0] = (uint32_t)(x >> 32); bq.v[1] = (uint32_t)x; }
-                    else bq = philox4x32_10(g, rep, step, PDA_SLOT_BG_D, seed, epoch);
-                    sv = poisson_itr(bq.v[0], bq.v[1], (double)(t_diff * bd->bg_dd_rate));
+                    if (S) { uint64_t x = sobol_next(S); p_hi = (uint32_t)(x >> 32); p_lo = (uint32_t)x; }
+                    else p_hi = bw.v[2];
+                    sv = poisson_itr(p_hi, p_lo, (double)(t_diff * bd->bg_dd_rate));
                     float bg_d;
                     if ((float)(int32_t)sv <= rf_id) bg_d = (float)(int32_t)sv;
-                    else bg_d = floorf(rf_id * u01(S ? (uint32_t)(sobol_next(S) >> 32) : bq.v[2]));
+                    else bg_d = floorf(rf_id * u01(S ? (uint32_t)(sobol_next(S) >> 32) : bw.v[3]));
                     f_i = floorf(f_if - bg_d - bg_a + 0.5f);
                 }
                 if (S) w.v[2] = (uint32_t)(sobol_next(S) >> 32);             /* curand_normal in drawE */

@@ -33,14 +33,21 @@ static inline philox4_t philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uin
     return r;
 }
 
-/* slot numbers (counter word c3) of the draw contract */
+/* slot numbers (counter word c3) of the draw contract (v2: one block per dwell step, plus one
+ * per step when the background path is on; no per-sample block) */
 enum {
-    PDA_SLOT_STEP = 0u, /* x0: next-state uniform, x1: dwell uniform, x2: normal word,
-                           x3: initial-state uniform (step 0 only) */
-    PDA_SLOT_BG_A = 1u, /* x0,x1: 64-bit word of the acceptor-background Poisson draw,
-                           x2: its fallback uniform */
-    PDA_SLOT_BG_D = 2u, /* same for the donor background */
-    PDA_SLOT_SEED = 3u  /* step 0 only: x0 | x1<<32 seeds the xor128 binomial stream */
+    PDA_SLOT_STEP = 0u, /* x0: next-state uniform, x1: dwell uniform, x2: normal word;
+                           step 0 only: x3 seeds the xor128 binomial stream (rk_seed(x3)), and the
+                           initial-state uniform is built from the low bytes of x0, x1, x2, which
+                           the uniforms above (top 24 bits of a word) do not use */
+    PDA_SLOT_BG = 1u    /* x0: high word of the acceptor-background Poisson draw (low word 0),
+                           x1: its fallback uniform, x2 / x3: the same for the donor background */
 };
+
+/* the initial-state word of step 0 */
+static inline uint32_t pda_init_word(const philox4_t *w)
+{
+    return ((w->v[0] & 0xffu) << 24) | ((w->v[1] & 0xffu) << 16) | ((w->v[2] & 0xffu) << 8) | 0x80u;
+}
 
 #endif

@@ -92,25 +92,23 @@ static unsigned long long curand(curandStateScrambledSobol64 *s)
     if (s->sobol) return sobol_next(s);
     if (s->seeded) { fprintf(stderr, "ref_shim: unexpected curand()\n"); abort(); }
     s->seeded = 1;
-    philox4_t w = philox4x32_10(s->g, s->rep, 0u, PDA_SLOT_SEED, s->seed, s->epoch);
-    return (unsigned long long)w.v[0] | ((unsigned long long)w.v[1] << 32);
+    philox4_t w = philox4x32_10(s->g, s->rep, 0u, PDA_SLOT_STEP, s->seed, s->epoch);
+    return (unsigned long long)w.v[3];
 }
 
 static float curand_uniform(curandStateScrambledSobol64 *s)
 {
     if (s->sobol) return shim_u01((uint32_t)(sobol_next(s) >> 32));   /* _curand_uniform(ull), curand_uniform.h:84-89 */
     if (s->phase == 3 && s->bg_calls > 0) { /* fallback uniform of draw_P_B_Tr */
-        philox4_t w = philox4x32_10(s->g, s->rep, s->step,
-                                    s->bg_calls == 1 ? PDA_SLOT_BG_A : PDA_SLOT_BG_D, s->seed,
-                                    s->epoch);
-        return shim_u01(w.v[2]);
+        philox4_t w = philox4x32_10(s->g, s->rep, s->step, PDA_SLOT_BG, s->seed, s->epoch);
+        return shim_u01(s->bg_calls == 1 ? w.v[1] : w.v[3]);
     }
     if (s->phase == 3) { /* a window without photons drew no E: next step starts here */
         s->step++;
         s->phase = 1;
     }
     philox4_t w = philox4x32_10(s->g, s->rep, s->step, PDA_SLOT_STEP, s->seed, s->epoch);
-    if (s->phase == 0) { s->phase = 1; return shim_u01(w.v[3]); }
+    if (s->phase == 0) { s->phase = 1; return shim_u01(pda_init_word(&w)); }
     if (s->phase == 1) { s->phase = 2; return shim_u01(w.v[0]); }
     s->phase = 3;
     s->bg_calls = 0;
@@ -160,9 +158,8 @@ static unsigned int curand_poisson(curandStateScrambledSobol64 *s, double lambda
     if (s->phase != 3 || s->bg_calls > 1) { fprintf(stderr, "ref_shim: poisson out of order\n"); abort(); }
     if (!(lambda < 1000.0)) { fprintf(stderr, "ref_shim: lambda >= 1000 outside contract\n"); abort(); }
     s->bg_calls++;
-    philox4_t w = philox4x32_10(s->g, s->rep, s->step,
-                                s->bg_calls == 1 ? PDA_SLOT_BG_A : PDA_SLOT_BG_D, s->seed, s->epoch);
-    return shim_poisson_itr(((uint64_t)w.v[0] << 32) | w.v[1], lambda);
+    philox4_t w = philox4x32_10(s->g, s->rep, s->step, PDA_SLOT_BG, s->seed, s->epoch);
+    return shim_poisson_itr((uint64_t)(s->bg_calls == 1 ? w.v[0] : w.v[2]) << 32, lambda);
 }
 
 /* ---- libdevice stand-ins -------------------------------------------------------- */
