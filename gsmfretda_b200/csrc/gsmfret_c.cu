@@ -543,7 +543,7 @@ int gsm_init_data(gsm_ctx* c, int64_t B, const int64_t* istart, const int64_t* s
     }
     if (pk_total >= (1ll << 34)) return fail(GSM_ERANGE, "%lld photon words: the packed offset covers 2^34", (long long)pk_total);
     if (with_bg && !(max_lambda < 900.0))
-        return fail(GSM_ERANGE, "background mean %g per burst: the Poisson draw contract covers lambda < 1000", max_lambda);
+        return fail(GSM_ERANGE, "background mean %g per burst: the Poisson draw contract covers lambda < 900", max_lambda);
     CK(cudaSetDevice(c->devid));
     for (Slot& s : c->slots) CK(cudaStreamSynchronize(s.stream));
     cudaFree(c->d_bursts); cudaFree(c->d_pk); cudaFree(c->d_pm); cudaFree(c->d_nx); cudaFree(c->d_cw);
@@ -677,6 +677,10 @@ int gsm_set_params(gsm_ctx* c, int n, int sid, const float* args, int n_args)
     if (r) return r;
     CK(cudaStreamSynchronize(s.stream));  // the staging buffer may still feed the previous run
     if (!expand_params(n, args, n_args, &s.h_params[0])) {
+        // the slot holds no vector now: a run on it is refused instead of evaluating the previous one
+        s.P = 0;
+        s.ran = false;
+        s.params_resident = false;
         fail(GSM_EINVAL, "set_params: %d values for %d states (need n*n+n, 2 <= n <= %d)", n_args, n, kMaxStates);
         return 0;
     }

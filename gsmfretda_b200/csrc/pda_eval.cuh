@@ -261,7 +261,7 @@ __device__ __forceinline__ void lane_save_reference(const Lane& L, const EvalArg
 // one dwell window (one trip of the reference's while loop, mc.cu:117-191)
 template <int kLayout, bool kBg, int kMode>
 __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const EvalArgs& a, uint32_t epoch,
-                                          const double2* __restrict__ ltab)
+                                          const double2* __restrict__ ltab, const double* __restrict__ rcp)
 {
     constexpr bool kFast = kMode == kModeNormal;
     constexpr bool kSobol = kMode == kModeReference;
@@ -366,10 +366,10 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
             // one block for both channels: x / z the high word of each Poisson draw (low word 0),
             // y / w the fall-back uniforms
             const u32x4 bw = philox4x32_10(g, L.rep, L.step, kSlotBg, a.seed, epoch);
-            uint32_t sv = poisson_itr(bw.x, 0u, (double)(t_diff * a.bg_ad_rate));
+            uint32_t sv = poisson_itr(bw.x, 0u, (double)(t_diff * a.bg_ad_rate), rcp);
             const float bg_a = ((float)(int32_t)sv <= rf_ia) ? (float)(int32_t)sv : floorf(rf_ia * u01(bw.y));
             const float rf_id = (kGamma - kDch2Ach) * (float)win.f_id;
-            sv = poisson_itr(bw.z, 0u, (double)(t_diff * a.bg_dd_rate));
+            sv = poisson_itr(bw.z, 0u, (double)(t_diff * a.bg_dd_rate), rcp);
             const float bg_d = ((float)(int32_t)sv <= rf_id) ? (float)(int32_t)sv : floorf(rf_id * u01(bw.w));
             f_i = floorf(f_if - bg_d - bg_a + 0.5f);
         }
@@ -569,8 +569,12 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
     // the {c_j, L_j} table of det_log (FP64 binomial): divergent lookups are bank conflicts here
     // instead of L1 sectors
     __shared__ double2 s_logtab[kMode == kModeNormal ? 1 : 128];
+    // RN(1/k), k <= 64, of the Poisson inversion (background path of the replay arithmetic)
+    __shared__ double s_rcp[(kBg && kMode == kModeReplay) ? 65 : 1];
     if (kMode != kModeNormal) {
         for (int i = threadIdx.x; i < 128; i += kBlock) s_logtab[i] = kLogTab[i];
+        if (kBg && kMode == kModeReplay)
+            for (int i = threadIdx.x; i < 65; i += kBlock) s_rcp[i] = kRcpSmallInt[i];
         __syncthreads();
     }
 
@@ -707,7 +711,7 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
 
         // ---- one dwell window for every active lane -------------------------------------
         if (active) {
-            lane_step<kLayout, kBg, kMode>(L, sp, a, wc.epoch, s_logtab);
+            lane_step<kLayout, kBg, kMode>(L, sp, a, wc.epoch, s_logtab, s_rcp);
             bool fin = !(L.T > L.spent);
             if (!fin && L.step >= kStepCap) {
                 atomicOr(a.counters + 2, 1ull);

@@ -296,6 +296,12 @@ class p_str {
 
 // message res { int32 ridx = 1; float e = 2; bool hist = 3; string idx = 4;
 //               repeated float shist = 5 [packed=true]; }               (args.proto:39-45)
+// Batch extension: when a p_ga reply carried P > 1 vectors
+// (params_size = P (n*n + n), indices idx .. idx + P - 1), the result message adds
+//               repeated float es = 6 [packed=true];   chi-square of every vector of the batch
+//               int32 best = 7;                         offset of the smallest one; e, hist, shist describe it
+// Both are absent for a single vector (proto3 writes no defaults), so the unbatched bytes are the
+// reference's; a server that does not know them skips them as unknown fields.
 class res {
   public:
     int32_t ridx() const { return ridx_; }
@@ -310,7 +316,12 @@ class res {
     void set_hist(bool v) { hist_ = v; }
     void set_idx(const std::string& v) { idx_ = v; }
     void add_shist(float v) { shist_.push_back(v); }
-    void Clear() { ridx_ = 0; e_ = 0.0f; hist_ = false; idx_.clear(); shist_.clear(); }
+    int es_size() const { return (int)es_.size(); }
+    float es(int i) const { return es_[(size_t)i]; }
+    void add_es(float v) { es_.push_back(v); }
+    int32_t best() const { return best_; }
+    void set_best(int32_t v) { best_ = v; }
+    void Clear() { ridx_ = 0; e_ = 0.0f; hist_ = false; idx_.clear(); shist_.clear(); es_.clear(); best_ = 0; }
     GSM_PB_COMMON(res)
   private:
     void append_to(std::string& o) const
@@ -320,6 +331,8 @@ class res {
         wire::put_bool(o, 3, hist_);
         wire::put_string(o, 4, idx_);
         wire::put_packed_floats(o, 5, shist_);
+        wire::put_packed_floats(o, 6, es_);
+        wire::put_int32(o, 7, best_);
     }
     void field(int f, int wt, wire::Reader& r)
     {
@@ -328,6 +341,8 @@ class res {
         else if (f == 3 && wt == 0) hist_ = r.varint() != 0;
         else if (f == 4) r.str(wt, idx_);
         else if (f == 5) r.floats(wt, shist_);
+        else if (f == 6) r.floats(wt, es_);
+        else if (f == 7 && wt == 0) best_ = (int32_t)r.varint();
         else r.skip(wt);
     }
     int32_t ridx_ = 0;
@@ -335,6 +350,8 @@ class res {
     bool hist_ = false;
     std::string idx_;
     std::vector<float> shist_;
+    std::vector<float> es_;
+    int32_t best_ = 0;
 };
 
 #undef GSM_PB_COMMON

@@ -45,18 +45,27 @@ class gpuWorker {
     }
 
   private:
-    // the six calls of gpuWorker.cpp:71-80, in the reference's order
+    // the six calls of gpuWorker.cpp:71-80, in the reference's order.  params[sid] holding a
+    // whole number P > 1 of vectors is a batch (streamWorker::fetch): staged with
+    // set_params_batch and evaluated by the same run_kernel in one launch.  A vector the library
+    // refuses (wrong count, n < 2) launches nothing; streamWorker reports it with chi2 = +inf.
     void launch(int sid)
     {
-        const int oldS_n = pdamc->set_nstates(s_n[sid], sid);
-        pdamc->set_params(s_n[sid], sid, params[sid]);
+        const int n = s_n[sid];
+        const int oldS_n = pdamc->set_nstates(n, sid);
+        const size_t per_vector = (size_t)n * (size_t)(n + 1);
+        const size_t have = params[sid].size();
+        if (per_vector > 0 && have > per_vector && have % per_vector == 0)
+            pdamc->set_params_batch(n, sid, (int)(have / per_vector), params[sid]);
+        else
+            pdamc->set_params(n, sid, params[sid]);
         const int N_sid = pdamc->setBurstBd(ga_start[sid], ga_stop[sid], sid);
         const bool n_changed = N_sid != N[sid];
         if (n_changed) {
             pdamc->init_randstate(N_sid, sid);
             N[sid] = N_sid;
         }
-        if (oldS_n != s_n[sid] || n_changed) pdamc->set_params_buff(oldS_n, N_sid, sid);
+        if (oldS_n != n || n_changed) pdamc->set_params_buff(oldS_n, N_sid, sid);
         pdamc->run_kernel(N[sid], sid);
     }
 

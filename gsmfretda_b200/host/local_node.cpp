@@ -20,7 +20,13 @@
 #include <sstream>
 #include <string>
 
-#include "gpuWorker.hpp"
+// GSM_GPUWORKER_HEADER: the drop-in proof (host/Makefile `dropin`, tests/test_host_cpp.py) points
+// this at a scratch copy of the REFERENCE's gpuWorker.hpp, whose gpuWorker.cpp is then compiled
+// unchanged against host/mc.hpp and linked in the place of this node's own gpuWorker
+#ifndef GSM_GPUWORKER_HEADER
+#define GSM_GPUWORKER_HEADER "gpuWorker.hpp"
+#endif
+#include GSM_GPUWORKER_HEADER
 
 struct Job { int idx; int n; std::vector<float> args; };
 

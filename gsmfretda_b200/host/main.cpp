@@ -21,13 +21,14 @@
 #include <cstdlib>
 #include <getopt.h>
 #include <iostream>
+#include <sstream>
 #include <thread>
 #include <vector>
 
 #include "gpuWorker.hpp"
 #include "loadHdf5.hpp"
 #include "streamWorker.hpp"
-#include "tools.hpp"
+#include "node_log.hpp"
 
 static void usage()
 {
@@ -111,10 +112,10 @@ int main(int argc, char* argv[])
             case 'g': gpuid = std::atoi(optarg); gpuid_given = true; break;
             case 'f': fretHistNum = std::atoi(optarg); break;
             case 'D': debuglevel = (unsigned char)~0; break;
-            case 'C': debuglevel |= debugLevel::cpu; break;
-            case 'G': debuglevel |= debugLevel::gpu; break;
-            case 'N': debuglevel |= debugLevel::net; break;
-            case 'K': debuglevel |= debugLevel::kernel; break;
+            case 'C': debuglevel |= node::kCpu; break;
+            case 'G': debuglevel |= node::kGpu; break;
+            case 'N': debuglevel |= node::kNet; break;
+            case 'K': debuglevel |= node::kKernel; break;
             case 'q': gpuinfo = true; break;
             case 'P': profiler = true; break;
             case 's': streamNum = std::atoi(optarg); break;

@@ -92,6 +92,9 @@ class mc {
         GSM_CHECK_RETURN(gsm_set_hist(ctx, opt.fret_hist_num, opt.left_pad));
         GSM_CHECK_RETURN(gsm_set_resample_times(ctx, reSampleTimes));
         streams = new cudaStream_t[streamNum];
+        bad_.assign((size_t)streamNum, 0);
+        batch_.assign((size_t)streamNum, 0);
+        batch_args_.resize((size_t)streamNum);
         hmcE = new retype*[streamNum]();
         s_n = new int[streamNum]();
         for (int i = 0; i < streamNum; ++i) streams[i] = (cudaStream_t)gsm_stream(ctx, i);
@@ -131,10 +134,14 @@ class mc {
         return r;  // the previous n (== n when unchanged), as mc::set_nstates
     }
 
+    // false when args has the wrong count for n states (eigenhelper.cpp:5-8); the slot is then
+    // marked failed: run_kernel launches nothing and failed(sid) tells the reader of the results
     bool set_params(int n, int sid, std::vector<float>& args)
     {
         int r = gsm_set_params(ctx, n, sid, args.data(), (int)args.size());
         GSM_CHECK_RETURN(r);
+        bad_[sid] = r != 1;
+        batch_[sid] = 0;
         return r == 1;
     }
 
@@ -163,7 +170,12 @@ class mc {
 
     void run_kernel(int N, int sid)
     {
-        GSM_CHECK_RETURN(gsm_run(ctx, N, sid));
+        if (bad_[sid]) return;   // the vector was refused: nothing to evaluate, the stream stays idle
+        if (batch_[sid] > 0) {
+            GSM_CHECK_RETURN(gsm_run_batch(ctx, N, sid, s_n[sid], batch_[sid], batch_args_[sid].data()));
+        } else {
+            GSM_CHECK_RETURN(gsm_run(ctx, N, sid));
+        }
         hmcE[sid] = const_cast<retype*>(gsm_result_mcE(ctx, sid));  // pinned; valid once streamQuery(sid)
     }
 
@@ -186,7 +198,23 @@ class mc {
 
     // ---- additions -------------------------------------------------------------------
     const uint64_t* hHist(int sid, int p = 0) const { return gsm_result_hist(ctx, sid, p); }
-    float hChi2(int sid) const { return gsm_result_chi2(ctx, sid); }
+    float hChi2(int sid, int p = 0) const
+    {
+        int P = 0;
+        const float* v = gsm_result_chi2v(ctx, sid, &P);
+        return (v && p >= 0 && p < P) ? v[p] : NAN;
+    }
+    bool failed(int sid) const { return bad_[sid]; }
+    // P vectors (each n*n + n values, back to back) for ONE launch: the next run_kernel(N, sid)
+    // evaluates them all (gsm_run_batch); results per vector through hChi2(sid, p) / hHist(sid, p),
+    // hmcE[sid] holds P blocks of N * reSampleTimes values
+    bool set_params_batch(int n, int sid, int P, const std::vector<float>& args)
+    {
+        bad_[sid] = n < 2 || P < 1 || (long long)args.size() != (long long)P * (n * n + n);
+        batch_[sid] = bad_[sid] ? 0 : P;
+        if (!bad_[sid]) batch_args_[sid] = args;
+        return !bad_[sid];
+    }
     gsm_ctx* handle() { return ctx; }
     // burst-split across GPUs, the all-reduce of the histogram fused into the evaluation kernel
     // (include/gsmfret_c.h: gsm_peer_*).  Every rank: peer_export, gather the handles in rank
@@ -200,4 +228,7 @@ class mc {
     gsm_ctx* ctx;
     int streamNum;
     cudaStream_t* streams;
+    std::vector<char> bad_;
+    std::vector<int> batch_;
+    std::vector<std::vector<float>> batch_args_;
 };

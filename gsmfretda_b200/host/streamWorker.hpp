@@ -1,31 +1,31 @@
-// streamWorker.hpp — the network side of one stream of the node: the REQ/REP conversation with
-// pySMFRETda's parameter server, same constructor, same `run(sid, sz_burst, leftPad)` and same
-// wire bytes as the reference's streamWorker (/root/reference/src/streamWorker.hpp:8-31,
-// streamWorker.cpp:39-245).  Every request is one opcode byte followed by a protobuf message
-// (args.proto):
+// streamWorker.hpp — the network side of one stream slot: the REQ/REP conversation with
+// pySMFRETda's parameter server.
 //
-//   dataready 0   'c' + p_cap{cap = sz_burst}            ->  p_n{s_n}                 -> 1
-//   dataready 1   'p' + p_str{str = node id, histNum,    ->  p_ga{idx, start, stop,   -> 2
-//                  ohist[] on the first request only}         bestfv, params[s_n(s_n+1)]}
-//                                                             idx == -1: nothing to do, ask again
-//                                                             idx == -2: leave
-//   dataready 2/3  (the gpuWorker thread launches and polls the evaluation; every 60 waits of
-//                  500 ms: 'k' + p_sid{sid = params_idx} -> any reply, keep-alive)
-//   dataready 4   'r' + res{ridx = params_idx, e = chi2, ->  p_sid{sid}; sid == -1: leave  -> 0
-//                  hist, idx = node id, shist[] = model
-//                  histogram / reSampleTimes when chi2 < bestfv}
+// Kept from the reference because other code binds to it: the class name, the constructor
+// (/root/reference/src/streamWorker.hpp:10-14), `run(sid, sz_burst, leftPad)`, the meaning of the
+// shared per-stream arrays and of the `dataready` values (0 need-capacity, 1 need-parameters,
+// 2 parameters-ready, 3 in flight, 4 results-ready; the gpuWorker thread moves 2 -> 3 -> 4), and
+// every byte on the wire (opcode + args.proto message, /root/reference/src/streamWorker.cpp:83-238):
 //
-// What differs from the reference is where the numbers come from, not what is sent: the model
-// histogram and the reduced chi-square are produced by the evaluation kernel itself
-// (mc::hHist / mc::hChi2, fused), so the N*R-float copy and the host histogram loop of
-// streamWorker.cpp:187-206 are gone.  `streamWorker::host_hist = true` brings that loop back —
-// hmcE -> regular-axis histogram -> chi-square on the host, the reference's exact arithmetic —
-// and tests/test_gpu_node.py checks both produce the same bytes on the wire.
+//   'c' + p_cap{cap}                       -> p_n{s_n}
+//   'p' + p_str{str, histNum, ohist[]}     -> p_ga{idx, start, stop, bestfv, params[]}
+//                                             idx -1: nothing to do now, ask again; idx -2: leave
+//   'k' + p_sid{sid = current idx}         -> anything            (keep-alive while the GPU works)
+//   'r' + res{ridx, e, hist, idx, shist[]} -> p_sid{sid}; sid -1: leave
+//
+// The body is this node's own: the conversation is a table of four handlers, one per state this
+// thread owns, over a small typed request/reply helper (`Link`).  Two things go beyond the
+// reference.  (1) The model histogram and the reduced chi-square come from the fused evaluation
+// kernel (mc::hHist / mc::hChi2); `host_hist = true` recomputes them on the host from hmcE with
+// the reference's arithmetic (tests/test_gpu_node.py holds both to the same wire bytes).
+// (2) Batches: a p_ga whose params[] holds P > 1 vectors (P (n*n + n) values, indices idx .. idx +
+// P - 1) is evaluated by ONE launch (mc::run_batch) and answered by one `res` that adds es[] and
+// best (args_pb.hpp); a single vector produces the reference's bytes exactly.
 #pragma once
-#include <cassert>
 #include <chrono>
 #include <cmath>
 #include <condition_variable>
+#include <limits>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -33,202 +33,263 @@
 
 #include "args_pb.hpp"
 #include "mc.hpp"
+#include "node_log.hpp"
 #include "sp_req.hpp"
-#include "tools.hpp"
+
+namespace node {
+
+// One REQ socket and typed round trips over it.
+class Link {
+  public:
+    explicit Link(const std::string& url)
+    {
+        fd_ = nn_socket(AF_SP, NN_REQ);
+        if (fd_ < 0) return;
+        int ms = 200;   // the reference's reconnect interval (streamWorker.cpp:48-49)
+        nn_setsockopt(fd_, NN_SOL_SOCKET, NN_RECONNECT_IVL, &ms, sizeof ms);
+        if (nn_connect(fd_, url.c_str()) < 0) {
+            nn_close(fd_);
+            fd_ = -1;
+        }
+    }
+    ~Link() { if (fd_ >= 0) nn_close(fd_); }
+    Link(const Link&) = delete;
+    Link& operator=(const Link&) = delete;
+    bool ok() const { return fd_ >= 0; }
+
+    // opcode byte + serialized request out, one message in; false = try the exchange again
+    template <class Request, class Reply>
+    bool ask(char opcode, const Request& rq, Reply* rp)
+    {
+        frame_.assign(1, opcode);
+        frame_ += rq.SerializeAsString();
+        if (nn_send(fd_, frame_.data(), frame_.size(), 0) < 0) return false;
+        char* in = nullptr;
+        const int got = nn_recv(fd_, &in, NN_MSG, 0);
+        if (got < 0) return false;
+        if (rp) rp->ParseFromArray(in, got);
+        nn_freemsg(in);
+        return true;
+    }
+
+  private:
+    int fd_ = -1;
+    std::string frame_;
+};
+
+// regular axis [lo, hi) with `bins` inner bins, underflow/overflow dropped: what the reference
+// builds with boost::histogram + indexed(coverage::inner) (streamWorker.cpp:33-38,62-67; bin rule
+// boost/histogram/axis/regular.hpp:292-308: z = (x - lo) / (hi - lo) in double, bin (int)(z bins))
+inline std::vector<float> inner_histogram(const float* x, size_t count, int bins, float lo, float hi)
+{
+    std::vector<float> h((size_t)bins, 0.0f);
+    const double span = (double)hi - (double)lo;
+    for (const float* it = x; it != x + count; ++it) {
+        const double z = ((double)*it - (double)lo) / span;
+        if (z >= 0.0 && z < 1.0) h[(size_t)(int)(z * bins)] += 1.0f;
+    }
+    return h;
+}
+
+// reduced chi-square of a model histogram against the observed one, the reference's host loop
+// (streamWorker.cpp:197-206), float accumulation included
+inline float reduced_chi2(const std::vector<float>& observed, const std::vector<float>& model, int R, int left_pad,
+                          int n_states)
+{
+    const int bins = (int)model.size();
+    int dof = bins - left_pad;
+    float sum = 0;
+    for (int b = left_pad; b < bins; ++b) {
+        if (model[(size_t)b] > 0)
+            sum += std::pow((float(observed[(size_t)b] - model[(size_t)b] / R)), 2) / (float(model[(size_t)b]) / R);
+        else
+            --dof;
+    }
+    return sum / (dof - n_states * (n_states + 1));
+}
+
+}  // namespace node
 
 class streamWorker {
   public:
     streamWorker(mc* _pdamc, std::string* _url, std::vector<float>* _d, int _fretHistNum, std::mutex* m,
                  std::condition_variable* cv, int* _dataready, int* _sn, std::vector<float>* _params,
                  int* _ga_start, int* _ga_stop, int* _N, unsigned char debugl = 0)
-        : pdamc(_pdamc), SgDivSr(_d), fretHistNum(_fretHistNum), url(_url), _m(m), _cv(cv),
-          dataready(_dataready), s_n(_sn), params(_params), debug(debugl), N(_N), ga_start(_ga_start),
-          ga_stop(_ga_stop) {}
+        : engine_(_pdamc), url_(_url), observed_values_(_d), bins_(_fretHistNum), slot_mutex_(m), slot_cv_(cv),
+          state_(_dataready), n_states_(_sn), vectors_(_params), range_lo_(_ga_start), range_hi_(_ga_stop),
+          bursts_(_N), log_mask_(debugl) {}
 
-    bool host_hist = false;     // true: the reference's host path (hmcE -> histogram -> chi-square)
-    int keepalive_every = 60;   // waits of 500 ms between two 'k' messages (streamWorker.cpp:165)
-    bool epoch_from_idx = false;  // draws of an evaluation keyed by the server's params_idx (reproducible)
+    bool host_hist = false;       // recompute histogram + chi-square on the host from hmcE (the reference's path)
+    int keepalive_every = 60;     // 500 ms waits between two 'k' messages (streamWorker.cpp:165)
+    bool epoch_from_idx = false;  // key the draws of an evaluation by the server's vector index (reproducible runs)
 
-    // boost::histogram regular axis [lv, uv) with binnum bins, inner bins only (role of mkhist +
-    // indexed(coverage::inner), streamWorker.cpp:33-38,62-67; bin rule of
-    // boost/histogram/axis/regular.hpp:292-308: z = (x - lv) / (uv - lv) in double,
-    // 0 <= z < 1 -> (int)(z * binnum); z >= 1 or NaN -> overflow, z < 0 -> underflow, both dropped)
+    // the reference's name for the observed-histogram helper, kept for callers and tests
     static std::vector<float> mkhist(const float* x, size_t n, int binnum, float lv, float uv)
     {
-        std::vector<float> h((size_t)binnum, 0.0f);
-        const double delta = (double)uv - (double)lv;
-        for (size_t i = 0; i < n; ++i) {
-            const double z = ((double)x[i] - (double)lv) / delta;
-            if (z < 1.0) {
-                if (z >= 0.0) h[(size_t)(int)(z * binnum)] += 1.0f;
-            }
-        }
-        return h;
+        return node::inner_histogram(x, n, binnum, lv, uv);
     }
 
     void run(int sid, int sz_burst, int leftPad)
     {
-        bool send_sHist = false;
-        bool sent_oHist = false;
-        float msg_bestcs = 3.1E32f;
-        unsigned long keepalivecount = 0;
-        int sock = nn_socket(AF_SP, NN_REQ);
-        assert(sock >= 0);
-        int reconnect_ivl = 200;
-        nn_setsockopt(sock, NN_SOL_SOCKET, NN_RECONNECT_IVL, &reconnect_ivl, sizeof(reconnect_ivl));
-        int nneo = nn_connect(sock, url->c_str());
-        assert(nneo >= 0);
-        (void)nneo;
-        std::string gpuNodeId;
-        genuid(&gpuNodeId, pdamc->devid, sid, pdamc->gpuuuid);
-        // observed histogram of SgDivSr, raw counts (streamWorker.cpp:61-67)
-        const std::vector<float> vOEHist = mkhist(SgDivSr->data(), SgDivSr->size(), fretHistNum, 0.0f, 1.0f);
-        bool ending = false;
-        int32_t params_idx = 0;
-        do {
-            std::unique_lock<std::mutex> lck(_m[sid], std::defer_lock);
-            if (!lck.try_lock()) continue;
-            char* rbuf = nullptr;
-            int bytes;
-            if (dataready[sid] == 0) {
-                gSMFRETda::pb::p_cap cap;
-                cap.set_cap(sz_burst);
-                std::string scap;
-                cap.SerializeToString(&scap);
-                scap = "c" + scap;
-                bytes = nn_send(sock, scap.c_str(), scap.length(), 0);
-                if (bytes == -1) continue;
-                bytes = nn_recv(sock, &rbuf, NN_MSG, 0);
-                if (bytes < 0) continue;
-                gSMFRETda::pb::p_n sn;
-                sn.ParseFromArray(rbuf, bytes);
-                nn_freemsg(rbuf);
-                s_n[sid] = sn.s_n();
-                dataready[sid] = 1;
-                continue;
+        Session s(*url_);
+        s.sid = sid;
+        s.capacity = sz_burst;
+        s.left_pad = leftPad;
+        s.name = node::stream_name(engine_->devid, sid, engine_->gpuuuid);
+        s.observed = node::inner_histogram(observed_values_->data(), observed_values_->size(), bins_, 0.0f, 1.0f);
+        if (s.link.ok()) {
+            // one handler per value of dataready[sid]; 2 and 3 belong to the GPU thread, this thread waits
+            static constexpr Handler table[5] = {&streamWorker::announce, &streamWorker::fetch, &streamWorker::wait_gpu,
+                                                 &streamWorker::wait_gpu, &streamWorker::report};
+            while (!s.leaving) {
+                std::unique_lock<std::mutex> hold(slot_mutex_[sid], std::try_to_lock);
+                if (!hold.owns_lock()) continue;   // the GPU thread is looking at the slot
+                const int st = state_[sid];
+                if (st < 0 || st > 4) break;
+                (this->*table[st])(s, hold);
             }
-            if (dataready[sid] == 1) {
-                gSMFRETda::pb::p_str gpuidStr;
-                gpuidStr.set_str(gpuNodeId);
-                if (!sent_oHist) {
-                    gpuidStr.set_histnum(fretHistNum);
-                    sent_oHist = true;
-                    for (float o : vOEHist) gpuidStr.add_ohist(o);
-                } else {
-                    gpuidStr.set_histnum(0);
-                }
-                std::string sgpuid;
-                gpuidStr.SerializeToString(&sgpuid);
-                sgpuid = "p" + sgpuid;
-                bytes = nn_send(sock, sgpuid.c_str(), sgpuid.length(), 0);
-                if (bytes == -1) continue;
-                AtomicWriter(debug, debugLevel::cpu) << "p" + gpuNodeId << '\n';
-                gSMFRETda::pb::p_ga ga;
-                bytes = nn_recv(sock, &rbuf, NN_MSG, 0);
-                if (bytes < 0) continue;
-                ga.ParseFromArray(rbuf, bytes);
-                nn_freemsg(rbuf);
-                const int pidx = ga.idx();
-                msg_bestcs = ga.bestfv();
-                if (pidx == -1) continue;   // the server has nothing for this stream right now
-                if (pidx == -2) break;      // the server is done
-                params_idx = pidx;
-                const int ps_n = s_n[sid] * (s_n[sid] + 1);
-                params[sid].resize((size_t)ps_n);
-                AtomicWriter(debug, debugLevel::net) << "params_idx recv: " << params_idx << '\n';
-                // a short params[] reads as zeros, like protobuf's repeated-field access would not:
-                // the reference indexes past the end; here the evaluation is skipped by set_params
-                for (int pi = 0; pi < ps_n; pi++) params[sid][(size_t)pi] = pi < ga.params_size() ? ga.params(pi) : 0.0f;
-                ga_start[sid] = ga.start();
-                ga_stop[sid] = ga.stop();
-                // (a host-side field of the stream slot; this thread holds _m[sid] and the GPU thread
-                // only touches the slot in states 2 and 3)
-                if (epoch_from_idx) gsm_set_epoch(pdamc->handle(), sid, (uint32_t)params_idx + 1u);
-                dataready[sid] = 2;
-                lck.unlock();
-                _cv[sid].notify_one();
-                continue;
-            }
-            using namespace std::chrono_literals;
-            if (!_cv[sid].wait_for(lck, 500ms, [this, sid] { return dataready[sid] == 4; })) {
-                AtomicWriter(debug, debugLevel::cpu) << dataready[sid] << " dataready !=4\n";
-                if (++keepalivecount % (unsigned long)keepalive_every == 0) {
-                    gSMFRETda::pb::p_sid pidx;
-                    pidx.set_sid(params_idx);
-                    std::string spidx;
-                    pidx.SerializeToString(&spidx);
-                    spidx = "k" + spidx;
-                    bytes = nn_send(sock, spidx.c_str(), spidx.length(), 0);
-                    if (bytes == -1) continue;
-                    if (nn_recv(sock, &rbuf, NN_MSG, 0) >= 0) nn_freemsg(rbuf);
-                }
-                continue;
-            }
-            AtomicWriter(debug, debugLevel::cpu) << dataready[sid] << " dataready ==4\n";
-            const int R = pdamc->reSampleTimes;
-            std::vector<float> vMcHist;
-            float chisqr;
-            if (host_hist) {
-                // the reference's host path, operation for operation (streamWorker.cpp:186-206)
-                vMcHist = mkhist(pdamc->hmcE[sid], (size_t)N[sid] * (size_t)R, fretHistNum, 0.0f, 1.0f);
-                int effN = fretHistNum - leftPad;
-                chisqr = 0;
-                for (int ihist = leftPad; ihist < fretHistNum; ihist++) {
-                    if (vMcHist[(size_t)ihist] > 0)
-                        chisqr += std::pow((float(vOEHist[(size_t)ihist] - vMcHist[(size_t)ihist] / R)), 2) /
-                                  (float(vMcHist[(size_t)ihist]) / R);
-                    else
-                        effN--;
-                }
-                chisqr = chisqr / (effN - s_n[sid] * (s_n[sid] + 1));
-            } else {
-                // fused: the kernel's histogram (u64 counts, inner bins first) and chi-square
-                const uint64_t* h = pdamc->hHist(sid);
-                vMcHist.resize((size_t)fretHistNum);
-                for (int i = 0; i < fretHistNum; ++i) vMcHist[(size_t)i] = (float)h[i];
-                chisqr = pdamc->hChi2(sid);
-            }
-            gSMFRETda::pb::res chi2res;
-            chi2res.set_idx(gpuNodeId);
-            chi2res.set_ridx(params_idx);
-            chi2res.set_e(chisqr);
-            if (chisqr < msg_bestcs) {
-                send_sHist = true;
-                for (float s : vMcHist) chi2res.add_shist(s / R);
-            } else {
-                send_sHist = false;
-            }
-            chi2res.set_hist(send_sHist);
-            std::string sres;
-            chi2res.SerializeToString(&sres);
-            bytes = nn_send(sock, ("r" + sres).c_str(), sres.length() + 1, 0);
-            if (bytes == -1) continue;
-            gSMFRETda::pb::p_sid gas;
-            AtomicWriter(debug, debugLevel::net) << chisqr << "\t params_idx send: " << params_idx << '\n';
-            bytes = nn_recv(sock, &rbuf, NN_MSG, 0);
-            if (bytes < 0) continue;
-            gas.ParseFromArray(rbuf, bytes);
-            AtomicWriter(debug, debugLevel::net) << params_idx << " p_sid recv: " << gas.sid() << '\n';
-            if (gas.sid() == -1) ending = true;
-            nn_freemsg(rbuf);
-            dataready[sid] = 0;
-        } while (!ending);
-        pdamc->workerNum--;   // tells the gpuWorker loop this stream has left (streamWorker.cpp:240)
-        nn_close(sock);
+        }
+        engine_->workerNum--;   // the GPU thread leaves its loop when every stream has left
     }
 
   private:
-    mc* pdamc;
-    std::vector<float>* SgDivSr;
-    int fretHistNum;
-    std::string* url;
-    std::mutex* _m;
-    std::condition_variable* _cv;
-    int* dataready;
-    int* s_n;
-    std::vector<float>* params;
-    unsigned char debug;
-    int* N;
-    int* ga_start;
-    int* ga_stop;
+    struct Session {
+        explicit Session(const std::string& url) : link(url) {}
+        node::Link link;
+        int sid = 0, capacity = 0, left_pad = 0;
+        std::string name;
+        std::vector<float> observed;
+        bool observed_sent = false;
+        bool leaving = false;
+        int32_t job = 0;           // index of the (first) vector in flight
+        int batch = 1;             // vectors in flight
+        float best_so_far = std::numeric_limits<float>::max();
+        unsigned long idle_waits = 0;
+    };
+    using Handler = void (streamWorker::*)(Session&, std::unique_lock<std::mutex>&);
+
+    // state 0: tell the server how many bursts this node holds, learn the number of states
+    void announce(Session& s, std::unique_lock<std::mutex>&)
+    {
+        gSMFRETda::pb::p_cap mine;
+        mine.set_cap(s.capacity);
+        gSMFRETda::pb::p_n model;
+        if (!s.link.ask('c', mine, &model)) return;
+        n_states_[s.sid] = model.s_n();
+        state_[s.sid] = 1;
+    }
+
+    // state 1: ask for work; the observed histogram rides on the first request only
+    void fetch(Session& s, std::unique_lock<std::mutex>& hold)
+    {
+        gSMFRETda::pb::p_str hello;
+        hello.set_str(s.name);
+        hello.set_histnum(s.observed_sent ? 0 : bins_);
+        if (!s.observed_sent)
+            for (float v : s.observed) hello.add_ohist(v);
+        gSMFRETda::pb::p_ga work;
+        const bool answered = s.link.ask('p', hello, &work);
+        s.observed_sent = true;       // written once, whether or not the reply arrived (as the reference)
+        if (!answered) return;
+        node::say(log_mask_, node::kCpu, "asked for work as %s\n", s.name.c_str());
+        s.best_so_far = work.bestfv();
+        if (work.idx() == -1) return;                     // nothing for this stream right now
+        if (work.idx() == -2) { s.leaving = true; return; }   // the optimisation is over
+        const int n = n_states_[s.sid];
+        const int per_vector = n * (n + 1);
+        // a batch is a whole number (> 1) of vectors; anything else is one vector, zero-padded or
+        // cut to size (the reference reads params(i) for i < n(n+1) whatever arrived)
+        int count = 1;
+        if (per_vector > 0 && work.params_size() > per_vector && work.params_size() % per_vector == 0)
+            count = work.params_size() / per_vector;
+        std::vector<float>& v = vectors_[s.sid];
+        v.assign((size_t)per_vector * (size_t)count, 0.0f);
+        for (int i = 0; i < (int)v.size() && i < work.params_size(); ++i) v[(size_t)i] = work.params(i);
+        s.job = work.idx();
+        s.batch = count;
+        range_lo_[s.sid] = work.start();
+        range_hi_[s.sid] = work.stop();
+        node::say(log_mask_, node::kNet, "vector %d (+%d) received\n", (int)s.job, count - 1);
+        // a host-side field of the slot: this thread holds the slot and the GPU thread only touches
+        // it in states 2 and 3
+        if (epoch_from_idx) gsm_set_epoch(engine_->handle(), s.sid, (uint32_t)s.job + 1u);
+        state_[s.sid] = 2;
+        hold.unlock();
+        slot_cv_[s.sid].notify_one();
+    }
+
+    // states 2 and 3: the GPU thread owns the slot; sleep until it posts the results, and let the
+    // server know now and then that this stream is alive
+    void wait_gpu(Session& s, std::unique_lock<std::mutex>& hold)
+    {
+        const int sid = s.sid;
+        if (slot_cv_[sid].wait_for(hold, std::chrono::milliseconds(500), [this, sid] { return state_[sid] == 4; })) return;
+        node::say(log_mask_, node::kCpu, "stream %d still waiting (state %d)\n", sid, state_[sid]);
+        if (++s.idle_waits % (unsigned long)keepalive_every != 0) return;
+        gSMFRETda::pb::p_sid alive;
+        alive.set_sid(s.job);
+        s.link.ask('k', alive, (gSMFRETda::pb::p_sid*)nullptr);
+    }
+
+    // state 4: send chi-square (and the model histogram when it beats the server's best)
+    void report(Session& s, std::unique_lock<std::mutex>&)
+    {
+        const int sid = s.sid;
+        const int R = engine_->reSampleTimes;
+        const int n = n_states_[sid];
+        const bool failed = engine_->failed(sid);   // the vector was refused (wrong size / n < 2): nothing ran
+        std::vector<float> chi(s.batch, std::numeric_limits<float>::infinity());
+        int best = 0;
+        if (!failed) {
+            for (int p = 0; p < s.batch; ++p) {
+                if (host_hist) {
+                    const size_t per = (size_t)bursts_[sid] * (size_t)R;
+                    chi[p] = node::reduced_chi2(s.observed, node::inner_histogram(engine_->hmcE[sid] + p * per, per, bins_, 0.0f, 1.0f),
+                                                R, s.left_pad, n);
+                } else {
+                    chi[p] = engine_->hChi2(sid, p);
+                }
+                if (chi[p] < chi[best]) best = p;
+            }
+        }
+        gSMFRETda::pb::res out;
+        out.set_idx(s.name);
+        out.set_ridx(s.job);
+        out.set_e(chi[best]);
+        const bool attach = !failed && chi[best] < s.best_so_far;
+        if (attach) {
+            if (host_hist) {
+                const size_t per = (size_t)bursts_[sid] * (size_t)R;
+                for (float c : node::inner_histogram(engine_->hmcE[sid] + best * per, per, bins_, 0.0f, 1.0f)) out.add_shist(c / R);
+            } else {
+                const uint64_t* counts = engine_->hHist(sid, best);
+                for (int b = 0; b < bins_; ++b) out.add_shist((float)counts[b] / R);
+            }
+        }
+        out.set_hist(attach);
+        if (s.batch > 1) {
+            for (float c : chi) out.add_es(c);
+            out.set_best(best);
+        }
+        gSMFRETda::pb::p_sid verdict;
+        if (!s.link.ask('r', out, &verdict)) return;     // same state: the result is sent again
+        node::say(log_mask_, node::kNet, "vector %d: chi2 %g sent, server says %d\n", (int)s.job, (double)chi[best],
+                  (int)verdict.sid());
+        if (verdict.sid() == -1) s.leaving = true;
+        state_[sid] = 0;
+    }
+
+    mc* engine_;
+    std::string* url_;
+    std::vector<float>* observed_values_;
+    int bins_;
+    std::mutex* slot_mutex_;
+    std::condition_variable* slot_cv_;
+    int* state_;
+    int* n_states_;
+    std::vector<float>* vectors_;
+    int* range_lo_;
+    int* range_hi_;
+    int* bursts_;
+    unsigned char log_mask_;
 };

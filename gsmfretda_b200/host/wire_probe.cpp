@@ -118,6 +118,8 @@ int main(int argc, char** argv)
                 else if (k == "hist") m.set_hist(std::atoi(v.c_str()) != 0);
                 else if (k == "idx") m.set_idx(v);
                 else if (k == "shist") for (auto& t : split(v, ',')) m.add_shist(parse_float(t));
+                else if (k == "es") for (auto& t : split(v, ',')) m.add_es(parse_float(t));
+                else if (k == "best") m.set_best(std::atoi(v.c_str()));
             });
         return 2;
     }
@@ -152,6 +154,12 @@ int main(int argc, char** argv)
             ok = m.ParseFromArray(b.data(), (int)b.size());
             std::printf("ridx=%d\ne=0x%08x\nhist=%d\nidx=%s\n", m.ridx(), fbits(m.e()), m.hist() ? 1 : 0, m.idx().c_str());
             print_floats("shist", m.shist());
+            if (m.es_size()) {
+                std::vector<float> es;
+                for (int i = 0; i < m.es_size(); ++i) es.push_back(m.es(i));
+                print_floats("es", es);
+                std::printf("best=%d\n", m.best());
+            }
         } else {
             return 2;
         }

@@ -48,8 +48,10 @@ def _build_messages():
     msg("p_cap", [("cap", 1, _F.TYPE_INT32, 0)])                     # :29-31
     msg("p_str", [("histNum", 1, _F.TYPE_INT32, 0), ("str", 2, _F.TYPE_STRING, 0),
                   ("ohist", 3, _F.TYPE_FLOAT, 1)])                   # :33-37
+    # :39-45, plus the batch extension of gsmfretda_b200/host/args_pb.hpp (es = 6, best = 7)
     msg("res", [("ridx", 1, _F.TYPE_INT32, 0), ("e", 2, _F.TYPE_FLOAT, 0), ("hist", 3, _F.TYPE_BOOL, 0),
-                ("idx", 4, _F.TYPE_STRING, 0), ("shist", 5, _F.TYPE_FLOAT, 1)])  # :39-45
+                ("idx", 4, _F.TYPE_STRING, 0), ("shist", 5, _F.TYPE_FLOAT, 1), ("es", 6, _F.TYPE_FLOAT, 1),
+                ("best", 7, _F.TYPE_INT32, 0)])
     pool = descriptor_pool.DescriptorPool()
     pool.Add(fdp)
     return {n: message_factory.GetMessageClass(pool.FindMessageTypeByName("gSMFRETda.pb." + n))
@@ -175,8 +177,10 @@ class RepServer:
 class ParamServer:
     """The four exchanges of the protocol over a RepServer."""
 
-    def __init__(self, n_states, vectors, bestfv=3.0e32, start=0, stop=-1, url=None, idle_first=0):
+    def __init__(self, n_states, vectors, bestfv=3.0e32, start=0, stop=-1, url=None, idle_first=0, batch=1):
         self.n_states = n_states
+        self.batch = int(batch)          # vectors per 'p' reply (> 1: the batch extension)
+        self.raw = []                    # every 'r' body as received (byte-level checks)
         self.vectors = [list(map(float, v)) for v in vectors]
         self.bestfv = float(bestfv)
         self.start, self.stop = start, stop
@@ -213,9 +217,11 @@ class ParamServer:
                 if self.next >= len(self.vectors):
                     return PB["p_ga"](idx=-2, bestfv=self.bestfv).SerializeToString()
                 i = self.next
-                self.next += 1
+                take = min(self.batch, len(self.vectors) - i)
+                self.next += take
+                flat = [x for v in self.vectors[i:i + take] for x in v]
                 return PB["p_ga"](idx=i, start=self.start, stop=self.stop, bestfv=self.bestfv,
-                                  params=self.vectors[i]).SerializeToString()
+                                  params=flat).SerializeToString()
             if op == b"k":                                    # streamWorker.cpp:165-181
                 m = PB["p_sid"]()
                 m.ParseFromString(data)
@@ -224,7 +230,13 @@ class ParamServer:
             if op == b"r":                                    # streamWorker.cpp:207-235
                 m = PB["res"]()
                 m.ParseFromString(data)
-                self.results[m.ridx] = {"e": m.e, "hist": m.hist, "idx": m.idx, "shist": list(m.shist)}
+                self.raw.append(bytes(data))
+                if len(m.es) > 1:       # one message for a whole batch: chi-square per vector, histogram of the best
+                    for k, e in enumerate(m.es):
+                        self.results[m.ridx + k] = {"e": e, "hist": m.hist and k == m.best, "idx": m.idx,
+                                                    "shist": list(m.shist) if k == m.best else []}
+                else:
+                    self.results[m.ridx] = {"e": m.e, "hist": m.hist, "idx": m.idx, "shist": list(m.shist)}
                 if m.hist and m.e < self.bestfv:
                     pass   # a GA server would adopt the new best value here; fixed for the tests
                 finished = len(self.results) >= len(self.vectors)

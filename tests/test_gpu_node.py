@@ -81,6 +81,50 @@ def test_node_from_hdf5_file_matches_the_oracle(world):
         srv.close()
 
 
+@pytest.mark.parametrize("extra", [(), ("--host-hist",)], ids=["fused", "host-hist"])
+def test_batched_p_ga_is_one_launch_per_batch_and_the_same_numbers(world, extra):
+    """Batch extension: the server packs 4 vectors into one p_ga; the node evaluates
+    them with one gsm_run_batch launch and answers with one `res` carrying es[] and best.  Every
+    chi-square equals the unbatched one bit for bit (draws keyed by the vector index); the
+    histogram attached is the best vector's of each batch."""
+    best = float(np.median([c for _, c in world["want"]]))
+    srv = ParamServer(2, world["vecs"], bestfv=best, batch=4)
+    try:
+        run_node(srv, os.path.join(H5, "from_bin.h5"), *extra, streams=2)
+        assert sorted(srv.results) == list(range(len(world["vecs"])))
+        assert len(srv.raw) == 3                                      # 9 vectors in batches of 4, 4, 1
+        for first in (0, 4, 8):
+            members = list(range(first, min(first + 4, 9)))
+            cs = [np.float32(world["want"][i][1]) for i in members]
+            k = int(np.argmin(cs))
+            for j, i in enumerate(members):
+                got = srv.results[i]
+                assert np.float32(got["e"]) == cs[j], (i, got["e"], cs[j])
+                attach = j == k and cs[k] < np.float32(best)
+                assert got["hist"] == attach
+                if attach:
+                    assert np.array_equal(np.array(got["shist"], np.float32),
+                                          world["want"][i][0][:NB].astype(np.float32) / np.float32(R))
+                else:
+                    assert got["shist"] == []
+    finally:
+        srv.close()
+
+
+def test_a_refused_vector_is_reported_not_evaluated(world):
+    """A vector the library refuses (here: the server announces 1 state, genMatK's empty rate list,
+    eigenhelper.cpp:5-8) launches nothing: chi-square +inf, no histogram — never the numbers of the
+    previous vector of that stream."""
+    srv = ParamServer(1, [[0.5, 2.0]] * 3, bestfv=3.0e32)
+    try:
+        run_node(srv, os.path.join(H5, "from_bin.h5"), streams=1)
+        assert sorted(srv.results) == [0, 1, 2]
+        for i in range(3):
+            assert srv.results[i]["e"] == float("inf") and srv.results[i]["hist"] is False and srv.results[i]["shist"] == []
+    finally:
+        srv.close()
+
+
 def test_host_histogram_path_sends_the_same_numbers(world):
     # --host-hist: hmcE copied back, histogram and chi-square on the host with the reference's
     # arithmetic (streamWorker.cpp:186-206) -> same bytes as the fused kernel's

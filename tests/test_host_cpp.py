@@ -36,6 +36,66 @@ def test_shim_declares_the_reference_members():
         assert member in src, member
 
 
+REF_SRC = "/root/reference/src"
+DROPIN = os.path.join(HOST, "dropin_node")
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(REF_SRC, "gpuWorker.cpp")), reason="the reference checkout lives on the build box only")
+def test_reference_gpuworker_compiles_unchanged_against_the_shim():
+    """Drop-in proof: /root/reference/src/gpuWorker.cpp + gpuWorker.hpp, byte for
+    byte as they lie in the reference, compile against host/mc.hpp (with compat/args.pb.h and
+    compat/tools.hpp for the two other headers they include) and link with libgsmfret.so into
+    local_node's main.  The binary travels to the GPU box, where the test below runs it."""
+    build()
+    if os.path.exists(DROPIN):
+        os.unlink(DROPIN)
+    r = subprocess.run(["make", "-s", "-C", HOST, "dropin"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert os.path.exists(DROPIN)
+    # it is the reference's class that was linked: its run() prints this line with -G (debug gpu)
+    syms = subprocess.run(["nm", "-C", DROPIN], capture_output=True, text=True).stdout
+    assert "gpuWorker::run(int)" in syms and "gpuWorker::gpuWorker(" in syms
+    strings = subprocess.run(["strings", DROPIN], capture_output=True, text=True).stdout
+    assert "gpu dataready ==3" in strings      # a literal of /root/reference/src/gpuWorker.cpp:50
+    r = subprocess.run([DROPIN], capture_output=True, text=True)
+    assert r.returncode == 2 and "usage" in r.stderr
+
+
+def _check_node_output(oracle, exe, tmp_path, streams):
+    w = synth.workload(4, n_bursts=1200, R=8, P=10)
+    b = w.bursts()
+    synth.save_bin(b, str(tmp_path / "b.bin"))
+    with open(tmp_path / "p.txt", "w") as f:
+        for a in w.args:
+            f.write("2 " + " ".join(repr(float(x)) for x in a) + "\n")
+        f.write("3 " + " ".join(repr(float(x)) for x in synth.workload(3).args[0]) + "\n")   # n changes mid-run
+    r = subprocess.run([exe, str(tmp_path / "b.bin"), str(tmp_path / "p.txt"), str(tmp_path / "o.txt"), str(streams), "8", "42"],
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    rows = [l.split() for l in open(tmp_path / "o.txt") if l.strip()]
+    assert len(rows) == 11
+    ohist = oracle.observed_hist(b, NB)
+    allargs = [(2, a) for a in w.args] + [(3, synth.workload(3).args[0])]
+    for row in rows:
+        ji, epoch, chi2 = int(row[0]), int(row[2]), float(row[3])
+        hist = np.array([int(x) for x in row[4:]], np.uint64)
+        n, a = allargs[ji]
+        o = oracle.eval(b, n, a, 8, 42, epoch)
+        oh = oracle.hist(o["mcE"], NB)
+        assert np.array_equal(hist, oh), (ji, epoch, int(hist.sum()), int(oh.sum()))
+        c = oracle.chi2(ohist, oh, NB, 8, LEFT_PAD, n)
+        assert abs(chi2 - c) <= 2e-6 * abs(c)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not os.path.exists(DROPIN), reason="host/dropin_node is built where the reference checkout is (make -C host dropin)")
+def test_reference_gpuworker_drives_the_library(oracle, tmp_path):
+    """The reference's own gpuWorker::run (compiled unchanged, see above) in local_node's place:
+    same results as the oracle, bit for bit, through set_nstates / set_params / setBurstBd /
+    init_randstate / set_params_buff / run_kernel / streamQuery as the reference issues them."""
+    _check_node_output(oracle, DROPIN, tmp_path, 3)
+
+
 @pytest.mark.gpu
 def test_local_node_matches_oracle(oracle, tmp_path):
     exe = build()

@@ -52,6 +52,9 @@ CASES = [
     ("res", dict(ridx=41, e=1.7320508, hist=True, idx="abcd-1-2-0-0", shist=[i / 4.0 for i in range(200)])),
     ("res", dict(ridx=0, e=float("inf"), hist=False, idx="x")),
     ("res", dict(ridx=3, e=float("nan"), hist=False, idx="")),
+    # batch extension: chi-square of every vector + offset of the best one
+    ("res", dict(ridx=8, e=0.5, hist=True, idx="n", shist=[1.0, 2.0], es=[2.5, 0.5, 7.0], best=1)),
+    ("res", dict(ridx=8, e=2.5, hist=False, idx="n", es=[2.5, 9.5], best=0)),
 ]
 
 
