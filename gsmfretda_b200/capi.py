@@ -19,6 +19,7 @@ GSM_KEEP_COUNTS = 2
 GSM_FORCE_RAW64 = 4
 GSM_NO_INDEX = 8
 GSM_NO_TIMING = 16
+GSM_PEER_SHARED_DEVICE = 32
 GSM_MODE_REPLAY = 0
 GSM_MODE_NORMAL = 1
 GSM_MODE_REFERENCE = 2
@@ -78,6 +79,7 @@ SIGNATURES = {
     "gsm_result_counts": (_i64p, [_ctx, C.c_int]),
     "gsm_result_steps": (_i32p, [_ctx, C.c_int]),
     "gsm_result_flags": (C.c_uint64, [_ctx, C.c_int]),
+    "gsm_result_timing": (C.c_int, [_ctx, C.c_int, _u64p]),
     "gsm_last_elapsed_ms": (C.c_float, [_ctx, C.c_int]),
     "gsm_launch_count": (C.c_uint64, [_ctx]),
     "gsm_comm_unique_id": (C.c_int, [C.c_void_p]),
@@ -126,10 +128,12 @@ class Mc:
     Extra (fused path): `hist(sid, p)`, `chi2(sid)`; `hmcE(sid)` needs keep_mce=True."""
 
     def __init__(self, devid: int = 0, streamNum: int = 16, keep_mce: bool = False,
-                 keep_counts: bool = False, force_raw64: bool = False, no_index: bool = False):
+                 keep_counts: bool = False, force_raw64: bool = False, no_index: bool = False,
+                 peer_shared_device: bool = False):
         self.lib = load()
         flags = (GSM_KEEP_MCE if keep_mce else 0) | (GSM_KEEP_COUNTS if keep_counts else 0) | \
-                (GSM_FORCE_RAW64 if force_raw64 else 0) | (GSM_NO_INDEX if no_index else 0)
+                (GSM_FORCE_RAW64 if force_raw64 else 0) | (GSM_NO_INDEX if no_index else 0) | \
+                (GSM_PEER_SHARED_DEVICE if peer_shared_device else 0)
         h = _ctx()
         self._h = None
         self._ck(self.lib.gsm_create(devid, streamNum, flags, C.byref(h)))
@@ -302,6 +306,16 @@ class Mc:
 
     def flags(self, sid: int) -> int:
         return int(self.lib.gsm_result_flags(self._h, sid))
+
+    def timing_ns(self, sid: int) -> np.ndarray:
+        """%globaltimer stamps of the last run's last block: start, posted, all peers seen, done."""
+        out = (C.c_uint64 * 4)()
+        self._ck(self.lib.gsm_result_timing(self._h, sid, out))
+        return np.array(list(out), dtype=np.uint64)
+
+    def stream_ptr(self, sid: int) -> int:
+        """The slot's cudaStream_t as an integer (torch.cuda.ExternalStream takes it)."""
+        return int(self.lib.gsm_stream(self._h, sid) or 0)
 
     def elapsed_ms(self, sid: int) -> float:
         return float(self.lib.gsm_last_elapsed_ms(self._h, sid))

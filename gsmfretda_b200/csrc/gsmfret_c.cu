@@ -80,6 +80,7 @@ constexpr int kNcclSum = 0;     // ncclSum
 // ------------------------------------------------------------------------------------
 struct ResultHeader {
     unsigned long long flags;
+    unsigned long long stamp[4];   // %globaltimer of the last block: start, posted, all seen, done
     unsigned long long reserved;
 };
 
@@ -170,7 +171,8 @@ struct PeerHandle {
     uint64_t ptr;
     uint64_t bytes;
     cudaIpcMemHandle_t ipc;   // 64 bytes
-    unsigned char pad[128 - 32 - sizeof(cudaIpcMemHandle_t)];
+    unsigned char uuid[16];   // the GPU, whatever index it has in the exporting process
+    unsigned char pad[128 - 32 - 16 - sizeof(cudaIpcMemHandle_t)];
 };
 static_assert(sizeof(PeerHandle) == GSM_PEER_HANDLE_BYTES, "peer handle is 128 bytes");
 constexpr uint32_t kPeerMagic = 0x47534d50u;  // "GSMP"
@@ -758,7 +760,7 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
         if (nbp != c->peer_nbp) return fail(GSM_ESTATE, "histogram size changed after gsm_peer_export");
         for (int rk = 0; rk < c->peer_world; ++rk) a.peer.block[rk] = c->peer_map[rk] + (size_t)sid * c->peer_slot_words;
         a.peer.stride = (unsigned long long)c->peer_cap_P * nbp;
-        a.peer.seq = ++s.peer_seq;
+        a.peer.seq = s.peer_seq + 1;   // committed below, once the launch is in the stream
         a.peer.world = c->peer_world;
         a.peer.rank = c->rank;
         a.peer.timeout_ms = c->peer_timeout_ms;
@@ -799,6 +801,7 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
     }
     CK(launch_eval(a, c->layout, c->with_bg, c->cfg, s.stream, c->mode));
     c->launches += 1;
+    if (c->peer_on) s.peer_seq = a.peer.seq;
     if (c->comm) {
         int e = g_nccl.AllReduce(s.d_whist, s.d_whist, (size_t)s.P * nbp, kNcclUint64, kNcclSum, c->comm, s.stream);
         if (e) return fail(GSM_ENCCL, "ncclAllReduce returned %s(%d)", g_nccl.GetErrorString ? g_nccl.GetErrorString(e) : "?", e);
@@ -905,6 +908,15 @@ const int32_t* gsm_result_steps(const gsm_ctx* c, int sid)
     if (!c || sid < 0 || sid >= (int)c->slots.size()) return nullptr;
     return c->slots[sid].h_steps;
 }
+int gsm_result_timing(const gsm_ctx* c, int sid, uint64_t out_ns[4])
+{
+    if (!c || !out_ns || sid < 0 || sid >= (int)c->slots.size()) return fail(GSM_EINVAL, "bad timing query");
+    if (!c->slots[sid].ran) return fail(GSM_ESTATE, "no run on stream %d yet", sid);
+    const ResultHeader* h = (const ResultHeader*)c->slots[sid].h_res;
+    for (int i = 0; i < 4; ++i) out_ns[i] = h->stamp[i];
+    return GSM_OK;
+}
+
 uint64_t gsm_result_flags(const gsm_ctx* c, int sid)
 {
     if (!c || sid < 0 || sid >= (int)c->slots.size() || !c->slots[sid].ran) return 0;
@@ -966,6 +978,8 @@ int gsm_peer_export(gsm_ctx* c, int world, int max_P, void* handle_out)
     if (!c || !handle_out || world < 1 || world > kMaxPeers || max_P < 1)
         return fail(GSM_EINVAL, "peer export: world %d (1..%d), max_P %d", world, kMaxPeers, max_P);
     if (c->comm) return fail(GSM_ESTATE, "an NCCL communicator is attached: use one reduction or the other");
+    // peers may have this block mapped and may be storing into it: it is only replaced after a disconnect
+    if (c->peer_on) return fail(GSM_ESTATE, "the peer exchange is connected: gsm_peer_disconnect first");
     CK(cudaSetDevice(c->devid));
     for (Slot& s : c->slots) CK(cudaStreamSynchronize(s.stream));
     peer_release(c);
@@ -980,6 +994,10 @@ int gsm_peer_export(gsm_ctx* c, int world, int max_P, void* handle_out)
     memset(&h, 0, sizeof(h));
     h.magic = kPeerMagic; h.pid = (uint32_t)getpid(); h.devid = c->devid; h.world = world;
     h.ptr = (uint64_t)(uintptr_t)c->peer_base; h.bytes = c->peer_bytes;
+    for (int i = 0; i < 16; ++i) {
+        auto nib = [](char ch) { return ch <= '9' ? ch - '0' : (ch | 0x20) - 'a' + 10; };
+        h.uuid[i] = (unsigned char)((nib(c->uuid[2 * i]) << 4) | nib(c->uuid[2 * i + 1]));
+    }
     CK(cudaIpcGetMemHandle(&h.ipc, c->peer_base));
     memcpy(handle_out, &h, sizeof(h));
     return GSM_OK;
@@ -992,6 +1010,38 @@ int gsm_peer_connect(gsm_ctx* c, const void* handles, int rank, int world)
     if (!c->peer_base || c->peer_world != world) return fail(GSM_ESTATE, "gsm_peer_export(world = %d) has not run", world);
     CK(cudaSetDevice(c->devid));
     const PeerHandle* hs = (const PeerHandle*)handles;
+    {
+        // Forward progress (include/gsmfret_c.h): ranks that share this GPU wait for each other inside
+        // their kernels, which only works while the GPU runs them concurrently.
+        PeerHandle me;
+        memcpy(&me, hs + rank, sizeof(me));
+        int same_gpu = 0, same_gpu_other_process = 0;
+        for (int r = 0; r < world; ++r) {
+            PeerHandle h;
+            memcpy(&h, hs + r, sizeof(h));
+            if (memcmp(h.uuid, me.uuid, 16) == 0) {
+                same_gpu++;
+                if (h.pid != me.pid) same_gpu_other_process++;
+            }
+        }
+        if (same_gpu > 1) {
+            if (!(c->flags & GSM_PEER_SHARED_DEVICE))
+                return fail(GSM_ESTATE, "%d ranks of this exchange share GPU %d: their kernels wait for each other and CUDA does "
+                            "not promise to run them concurrently; use one rank per GPU, gsm_comm_init, or create the "
+                            "contexts with GSM_PEER_SHARED_DEVICE", same_gpu, c->devid);
+            // ranks of other processes on this GPU: progress then rests on the driver's time-slicing
+            // between contexts (or MPS) — slow but live; the caller vouched for it with the flag
+            (void)same_gpu_other_process;
+            const char* lb = getenv("CUDA_LAUNCH_BLOCKING");
+            if (lb && atoi(lb) != 0) return fail(GSM_ESTATE, "CUDA_LAUNCH_BLOCKING serialises the ranks that share GPU %d", c->devid);
+            const char* mc = getenv("CUDA_DEVICE_MAX_CONNECTIONS");
+            const int queues = mc && atoi(mc) > 0 ? atoi(mc) : 8;
+            if ((long long)same_gpu * (long long)c->slots.size() > queues)
+                return fail(GSM_ESTATE, "%d ranks x %d stream slots on GPU %d exceed its %d hardware queues "
+                            "(CUDA_DEVICE_MAX_CONNECTIONS): launches would queue behind the kernels that wait for them",
+                            same_gpu, (int)c->slots.size(), c->devid, queues);
+        }
+    }
     for (int r = 0; r < world; ++r) {
         PeerHandle h;
         memcpy(&h, hs + r, sizeof(h));

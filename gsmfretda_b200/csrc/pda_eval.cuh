@@ -513,7 +513,8 @@ __device__ __forceinline__ unsigned long long global_ns()
 // partial bins into every rank's inbox over NVLink, release an arrival flag, wait for the
 // flags of all senders in the LOCAL block (no polling across the link), sum in rank order.
 // Integer bins: the sum does not depend on arrival order, so every rank holds identical bits.
-__device__ __forceinline__ void peer_exchange_block(const EvalArgs& a)
+// stamp[1] / stamp[2]: %globaltimer when this rank's flags were posted / when every flag had arrived
+__device__ __forceinline__ void peer_exchange_block(const EvalArgs& a, unsigned long long* stamp)
 {
     const PeerArgs& pe = a.peer;
     const int nbp = a.nb + 2;
@@ -528,6 +529,7 @@ __device__ __forceinline__ void peer_exchange_block(const EvalArgs& a)
     __syncthreads();
     if ((int)threadIdx.x < pe.world)
         st_release_sys(pe.block[threadIdx.x] + par * kMaxPeers + pe.rank, (unsigned long long)pe.seq);
+    if (threadIdx.x == 0) stamp[1] = global_ns();
     if ((int)threadIdx.x < pe.world) {
         const unsigned long long* f = pe.block[pe.rank] + par * kMaxPeers + threadIdx.x;
         const unsigned long long t0 = global_ns();
@@ -540,6 +542,7 @@ __device__ __forceinline__ void peer_exchange_block(const EvalArgs& a)
         }
     }
     __syncthreads();
+    if (threadIdx.x == 0) stamp[2] = global_ns();
     const unsigned long long* in = pe.block[pe.rank] + kPeerFlagWords + (size_t)par * pe.world * pe.stride;
     for (size_t i = threadIdx.x; i < tot; i += blockDim.x) {
         unsigned long long s = 0ull;
@@ -760,9 +763,17 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
     __syncthreads();
     if (s_last) {
         __threadfence();
+        __shared__ unsigned long long s_stamp[4];
+        if (threadIdx.x == 0) s_stamp[0] = s_stamp[1] = s_stamp[2] = global_ns();
         if (a.finalize) {
-            if (a.finalize == 2) peer_exchange_block(a);
+            if (a.finalize == 2) peer_exchange_block(a, s_stamp);
             finalize_block(a, reinterpret_cast<double*>(s_hist_all));   // every warp has flushed its bins
+            if (threadIdx.x == 0) {
+                a.flags_out[1] = s_stamp[0];
+                a.flags_out[2] = s_stamp[1];
+                a.flags_out[3] = s_stamp[2];
+                a.flags_out[4] = global_ns();
+            }
         } else if (threadIdx.x == 0) {
             a.counters[0] = 0ull;
             a.counters[1] = 0ull;

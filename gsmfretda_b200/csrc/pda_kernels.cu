@@ -25,7 +25,12 @@ namespace pda {
 __global__ void __launch_bounds__(kBlock) pda_finalize_kernel(const __grid_constant__ EvalArgs a)
 {
     extern __shared__ __align__(16) unsigned char s_raw[];   // nb doubles
+    const unsigned long long t0 = global_ns();
     finalize_block(a, reinterpret_cast<double*>(s_raw));
+    if (threadIdx.x == 0) {   // stamps of gsm_result_timing: no in-kernel exchange on this path
+        a.flags_out[1] = t0; a.flags_out[2] = t0; a.flags_out[3] = t0;
+        a.flags_out[4] = global_ns();
+    }
 }
 
 // ------------------------------------------------------------------------------------

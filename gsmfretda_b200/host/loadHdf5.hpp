@@ -50,8 +50,14 @@ inline bool load_bin(const std::string& fn, std::vector<int64_t>& start, std::ve
     std::vector<int> ph;
     std::vector<int64_t> ad, dd;
     bool ok = fread(magic, 1, 4, f) == 4 && !std::memcmp(magic, "GSMB", 4) && fread(&ver, 4, 1, f) == 1 && ver == 1 &&
-              fread(&B, 8, 1, f) == 1 && fread(&Nph, 8, 1, f) == 1 && fread(hdr, 4, 4, f) == 4 && B >= 0 && Nph >= 0 &&
-              rd(f, start, (size_t)B) && rd(f, stop, (size_t)B) && rd(f, istart, (size_t)B) && rd(f, ph, (size_t)B) &&
+              fread(&B, 8, 1, f) == 1 && fread(&Nph, 8, 1, f) == 1 && fread(hdr, 4, 4, f) == 4 && B >= 0 && Nph >= 0;
+    if (ok) {
+        // the header may promise no more than the file holds: 36 bytes per burst, 16 per photon
+        struct stat st;
+        ok = ::fstat(fileno(f), &st) == 0 && B <= (int64_t)st.st_size / 36 && Nph <= (int64_t)st.st_size / 16 &&
+             40 + 36 * B + 16 * Nph <= (int64_t)st.st_size;
+    }
+    ok = ok && rd(f, start, (size_t)B) && rd(f, stop, (size_t)B) && rd(f, istart, (size_t)B) && rd(f, ph, (size_t)B) &&
               rd(f, T, (size_t)B) && rd(f, SgDivSr, (size_t)B) && rd(f, ad, (size_t)Nph) && rd(f, dd, (size_t)Nph);
     std::fclose(f);
     if (!ok) return false;
@@ -59,7 +65,10 @@ inline bool load_bin(const std::string& fn, std::vector<int64_t>& start, std::ve
     bg_ad = hdr[1];
     bg_dd = hdr[2];
     istop.resize((size_t)B);
-    for (int64_t b = 0; b < B; ++b) istop[(size_t)b] = istart[(size_t)b] + ph[(size_t)b] - 1;
+    for (int64_t b = 0; b < B; ++b) {
+        if (ph[(size_t)b] < 0 || istart[(size_t)b] < 0 || istart[(size_t)b] > Nph - ph[(size_t)b]) return false;
+        istop[(size_t)b] = istart[(size_t)b] + ph[(size_t)b] - 1;
+    }
     times.resize((size_t)Nph);
     mask_ad.resize((size_t)Nph);
     mask_dd.resize((size_t)Nph);
@@ -126,7 +135,21 @@ inline void burst_data(std::vector<int64_t>& istart, std::vector<int64_t>& istop
 {
     const size_t sz_burst = istart.size();
     if (phCount.size() != sz_burst) phCount.resize(sz_burst);
-    for (size_t idx = 0; idx < sz_burst; idx++) phCount[idx] = (int)(istop[idx] - istart[idx] + 1);
+    // istart / istop come from the file: every burst must lie inside the photon arrays (all three
+    // of them) and its count must fit the int the reference keeps it in, before anything is indexed
+    const int64_t n_ph = (int64_t)times_ms.size();
+    if (istop.size() != sz_burst || (int64_t)mask_ad.size() != n_ph || (int64_t)mask_dd.size() != n_ph) {
+        std::cerr << "burst_data: istart/istop or times/mask_ad/mask_dd differ in length" << std::endl;
+        std::exit(EXIT_FAILURE);
+    }
+    for (size_t idx = 0; idx < sz_burst; idx++) {
+        const int64_t a = istart[idx], z = istop[idx];
+        if (a < 0 || z < a - 1 || z >= n_ph || z - a + 1 > 0x7fffffff) {
+            std::cerr << "burst_data: burst " << idx << " claims photons [" << a << ", " << z << "] of " << n_ph << std::endl;
+            std::exit(EXIT_FAILURE);
+        }
+        phCount[idx] = (int)(z - a + 1);
+    }
     // value-initialised: photons between bursts (not covered by any istart..istop) read as 0,
     // where the reference leaves them uninitialised (loadHdf5.cpp:112-113)
     *burst_ad = new int64_t[times_ms.size()]();

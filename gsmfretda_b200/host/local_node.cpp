@@ -79,7 +79,7 @@ int main(int argc, char** argv)
             if (ji >= (int)jobs.size()) break;
             { std::unique_lock<std::mutex> lck(_m[sid]);
               s_n[sid] = jobs[ji].n; params[sid] = jobs[ji].args; ga_start[sid] = 0; ga_stop[sid] = -1;
-              gsm_set_epoch(pdamc.handle(), sid, (uint32_t)(1000 + ji));
+              pdamc.set_epoch(sid, (uint32_t)(1000 + ji));
               dataready[sid] = 2; }
             _cv[sid].notify_one();
             { std::unique_lock<std::mutex> lck(_m[sid]);

@@ -6,7 +6,8 @@
 //
 // Additions (long options only, none changes the defaults):
 //   --resample-times R   Monte-Carlo repeats per burst (reference: fixed 4, mc.hpp:88)
-//   --mode replay|normal|reference evaluation arithmetic / draw source; default normal;
+//   --mode replay|normal|reference evaluation arithmetic / draw source; default replay
+//          (bit-exact against the checker; normal = FP32 fast arithmetic, statistically equivalent, ~1.3x faster);
 //          reference = the reference's own Sobol64 + xor128 generators: results equal the reference's bit for bit
 //   --seed S             seed of the counter-based generator
 //   --epoch-from-idx     draw stream of an evaluation = f(seed, params_idx) instead of the order
@@ -38,7 +39,8 @@ static void usage()
         "  -V, --version             Print version and exit\n"
         "  -u, --url=STRING          params server url tcp://ip:port  (default=`tcp://127.0.0.1:7777')\n"
         "  -i, --input=STRING        Input HDF5 filename\n"
-        "  -g, --gpuid=INT           The index of the GPU will be used  (default=`0')\n"
+        "  -g, --gpuid=INT[,INT...]  The index of the GPU will be used  (default=`0'); a list = one node\n"
+        "                            over several GPUs, the bursts split between them\n"
         "  -f, --fret_hist_num=INT   fret hist Number  (default=`200')\n"
         "  -D, --debug               Turn on all debug info  (default=off)\n"
         "  -C, --debugcpu            CPU debug info  (default=off)\n"
@@ -51,10 +53,12 @@ static void usage()
         "  -p, --parameters=FLOAT    Calculate with the parameters. Give them like -p 0.34,0.56,455,673,2,4\n"
         "  -I, --pid=STRING          Appoint a pid file\n"
         "      --resample-times=INT  Monte-Carlo repeats per burst  (default=`4')\n"
-        "      --mode=STRING         replay|normal|reference  (default=`normal')\n"
+        "      --mode=STRING         replay|normal|reference  (default=`replay')\n"
         "      --seed=INT            generator seed\n"
         "      --epoch-from-idx      reproducible draws per parameter index  (default=off)\n"
-        "      --host-hist           host histogram and chi-square, as the reference  (default=off)\n";
+        "      --host-hist           host histogram and chi-square, as the reference  (default=off)\n"
+        "      --max-batch=INT       most vectors per batched p_ga when the node spans GPUs  (default=`64')\n"
+        "      --oversubscribe       allow a GPU to appear twice in -g (test rigs)  (default=off)\n";
 }
 
 static void writepid(const std::string& fn)   // main.cpp:53-64
@@ -86,9 +90,10 @@ static int show_gpus(int only)   // role of showGPUsInfo (mc.cu:26-59) through t
 
 int main(int argc, char* argv[])
 {
-    std::string url = "tcp://127.0.0.1:7777", input, pidfile, mode = "normal";
-    int gpuid = 0, fretHistNum = 200, streamNum = 0, R = 4;
-    bool gpuid_given = false, gpuinfo = false, profiler = false, epoch_from_idx = false, host_hist = false;
+    std::string url = "tcp://127.0.0.1:7777", input, pidfile, mode = "replay";
+    int gpuid = 0, fretHistNum = 200, streamNum = 0, R = 4, max_batch = 64;
+    std::vector<int> gpu_list;   // -g 0,1,2: ONE node over several GPUs (the dataset is split)
+    bool gpuid_given = false, gpuinfo = false, profiler = false, epoch_from_idx = false, host_hist = false, oversubscribe = false;
     unsigned char debuglevel = 0;
     uint32_t seed = 0x9E3779B9u;
     std::vector<float> one_vector;
@@ -101,7 +106,8 @@ int main(int argc, char* argv[])
         {"snum", required_argument, 0, 's'}, {"parameters", required_argument, 0, 'p'},
         {"pid", required_argument, 0, 'I'}, {"resample-times", required_argument, 0, 1000},
         {"mode", required_argument, 0, 1001}, {"seed", required_argument, 0, 1002},
-        {"epoch-from-idx", no_argument, 0, 1003}, {"host-hist", no_argument, 0, 1004}, {0, 0, 0, 0}};
+        {"epoch-from-idx", no_argument, 0, 1003}, {"host-hist", no_argument, 0, 1004},
+        {"oversubscribe", no_argument, 0, 1005}, {"max-batch", required_argument, 0, 1006}, {0, 0, 0, 0}};
     int c;
     while ((c = getopt_long(argc, argv, "hVu:i:g:f:DCGNKqPs:p:I:", lo, nullptr)) != -1) {
         switch (c) {
@@ -109,7 +115,15 @@ int main(int argc, char* argv[])
             case 'V': std::cout << "gSMFRETda 1.0.0\n"; return EXIT_SUCCESS;
             case 'u': url = optarg; break;
             case 'i': input = optarg; break;
-            case 'g': gpuid = std::atoi(optarg); gpuid_given = true; break;
+            case 'g': {   // one id as in the reference, or a comma-separated list: one node spanning those GPUs
+                gpu_list.clear();
+                std::stringstream ss(optarg);
+                std::string t;
+                while (std::getline(ss, t, ',')) if (!t.empty()) gpu_list.push_back(std::atoi(t.c_str()));
+                gpuid = gpu_list.empty() ? 0 : gpu_list[0];
+                gpuid_given = true;
+                break;
+            }
             case 'f': fretHistNum = std::atoi(optarg); break;
             case 'D': debuglevel = (unsigned char)~0; break;
             case 'C': debuglevel |= node::kCpu; break;
@@ -131,6 +145,11 @@ int main(int argc, char* argv[])
             case 1002: seed = (uint32_t)std::strtoul(optarg, nullptr, 0); break;
             case 1003: epoch_from_idx = true; break;
             case 1004: host_hist = true; break;
+            case 1005:   // a GPU listed twice in -g: its parts wait for each other inside the device (gsm_peer_connect)
+                oversubscribe = true;
+                setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);   // before the first CUDA call
+                break;
+            case 1006: max_batch = std::atoi(optarg); break;
             default: return EXIT_FAILURE;
         }
     }
@@ -174,12 +193,25 @@ int main(int argc, char* argv[])
     opt.seed = seed;
     opt.fret_hist_num = fretHistNum;
     opt.left_pad = 2;                  // main.cpp:155
-    mc pdamc(gpuid, streamNum, debuglevel, hdf5size, profiler, opt);
+    opt.peer_shared_device = oversubscribe;
+    opt.max_batch = max_batch;         // most vectors one batched p_ga may carry when the node spans GPUs
+    if (gpu_list.empty()) gpu_list.push_back(gpuid);
+    if (gpu_list.size() > 1 && host_hist) {
+        std::cout << "--host-hist reads per-sample efficiencies of one GPU: not available with a GPU list" << std::endl;
+        return EXIT_FAILURE;
+    }
+    mc pdamc(gpu_list, streamNum, debuglevel, hdf5size, profiler, opt);
     pdamc.getStreams(&streamNum);      // streamNum = 0 asked for the automatic choice
     std::cout << "streamNum: " << streamNum << std::endl;
     if (streamNum <= 0) return EXIT_FAILURE;
     pdamc.set_reSampleTimes_exact(R);
-    GSM_CHECK_RETURN(gsm_set_mode(pdamc.handle(), mode == "replay" ? GSM_MODE_REPLAY : (mode == "reference" ? GSM_MODE_REFERENCE : GSM_MODE_NORMAL)));
+    pdamc.set_mode(mode == "replay" ? GSM_MODE_REPLAY : (mode == "reference" ? GSM_MODE_REFERENCE : GSM_MODE_NORMAL));
+    std::cout << "mode: " << mode << (mode == "replay" ? " (explicit-rounding arithmetic on counter-based draws: results are a pure function of data, parameters, seed and draw epoch, bit-equal to the checker)"
+                                      : mode == "normal" ? " (FP32 fast arithmetic on the same draws: statistically equivalent to replay, not bit-equal)"
+                                                         : " (the reference's own Sobol64/xor128 generators: bit-equal to the reference's GPU run)")
+              << "; GPUs:";
+    for (int g : gpu_list) std::cout << ' ' << g;
+    std::cout << std::endl;
     pdamc.init_data_gpu(istart, start, stop, phCount, (long)times_ms.size(), burst_ad, burst_dd, T_burst_duration,
                         SgDivSr, clk_p, bg_ad_rate, bg_dd_rate);
 

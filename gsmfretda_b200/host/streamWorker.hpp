@@ -212,7 +212,7 @@ class streamWorker {
         node::say(log_mask_, node::kNet, "vector %d (+%d) received\n", (int)s.job, count - 1);
         // a host-side field of the slot: this thread holds the slot and the GPU thread only touches
         // it in states 2 and 3
-        if (epoch_from_idx) gsm_set_epoch(engine_->handle(), s.sid, (uint32_t)s.job + 1u);
+        if (epoch_from_idx) engine_->set_epoch(s.sid, (uint32_t)s.job + 1u);
         state_[s.sid] = 2;
         hold.unlock();
         slot_cv_[s.sid].notify_one();

@@ -39,3 +39,41 @@ def split_population(P: int, world: int):
         out.append((p, p + n))
         p += n
     return out
+
+
+def vector_cost(n: int, args, mean_T: float = 2.0e-3, mean_photons: float = 60.0):
+    """Rough relative cost of one burst-sample under parameter vector `args` (layout of
+    mc::set_params: E | K off-diagonal, row-major | v): photons walked plus dwell segments, the
+    latter from the stationary exit flux of K times the mean burst duration.  Only the ORDER of the
+    costs matters to deal_population."""
+    a = np.asarray(args, dtype=np.float64)
+    k = a[n:n + n * n - n]
+    Q = np.zeros((n, n))
+    it = iter(k)
+    for i in range(n):
+        for j in range(n):
+            if i != j:
+                Q[i, j] = next(it)
+    q = Q.sum(axis=1)
+    A = (Q - np.diag(q)).T
+    A[-1, :] = 1.0
+    rhs = np.zeros(n)
+    rhs[-1] = 1.0
+    try:
+        pi = np.linalg.solve(A, rhs)
+    except np.linalg.LinAlgError:
+        pi = np.full(n, 1.0 / n)
+    flux = float(np.dot(np.clip(pi, 0.0, 1.0), q))
+    return 6.0 * mean_photons + (80.0 + 6.0 * n) * (1.0 + flux * mean_T)
+
+
+def deal_population(costs, world: int):
+    """-> one index array per rank: the vectors sorted by descending cost and dealt in snake order
+    (0..w-1, w-1..0, ...), so that every rank's share costs about the same although the vectors do
+    not (a vector with fast interconversion walks many more dwell segments per burst)."""
+    order = np.argsort(-np.asarray(costs, dtype=np.float64), kind="stable")
+    shares = [[] for _ in range(world)]
+    for pos, idx in enumerate(order):
+        rnd, k = divmod(pos, world)
+        shares[k if rnd % 2 == 0 else world - 1 - k].append(int(idx))
+    return [np.array(sorted(s), dtype=np.int64) for s in shares]

@@ -116,6 +116,23 @@ def make_bursts(n_bursts: int, E_states, seed: int, bg_ad_rate: float = 0.0,
                   bg_ad_rate=np.float32(bg_ad_rate), bg_dd_rate=np.float32(bg_dd_rate))
 
 
+def concat(blocks) -> Bursts:
+    """One dataset from several blocks of bursts, in order (istart rebased block by block).  The
+    blocks keep their own time axes: nothing downstream needs start_b to increase across blocks."""
+    blocks = list(blocks)
+    if len(blocks) == 1:
+        return blocks[0]
+    off, ist = 0, []
+    for b in blocks:
+        ist.append(b.istart + off)
+        off += b.n_photons
+    cat = lambda name: np.concatenate([getattr(b, name) for b in blocks])
+    b0 = blocks[0]
+    return Bursts(start=cat("start"), stop=cat("stop"), istart=np.concatenate(ist), ph_count=cat("ph_count"),
+                  T=cat("T"), burst_ad=cat("burst_ad"), burst_dd=cat("burst_dd"), SgDivSr=cat("SgDivSr"),
+                  clk_p=b0.clk_p, bg_ad_rate=b0.bg_ad_rate, bg_dd_rate=b0.bg_dd_rate)
+
+
 def pack_args(E, k_offdiag_rowmajor, v) -> np.ndarray:
     """args = [E_0..E_{n-1} | k (n*n-n, row-major without the diagonal) | v_0..v_{n-1}],
     the vector `mc::set_params` splits (/root/reference/src/mc.cu:792-799)."""

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define GSM_ABI_VERSION 1
+#define GSM_ABI_VERSION 2
 
 #define GSM_OK 0
 #define GSM_EINVAL (-1)    /* bad argument */
@@ -48,6 +48,8 @@ extern "C" {
 #define GSM_NO_INDEX 8u     /* packed photons without the window index: photon-by-photon scan */
 #define GSM_NO_TIMING 16u   /* do not bracket every run with CUDA events (gsm_last_elapsed_ms returns -1):
                                two driver calls less per evaluation, for nodes that evaluate small bursts sets */
+#define GSM_PEER_SHARED_DEVICE 32u /* the caller vouches that ranks of one peer exchange that share a GPU run
+                               concurrently there (see gsm_peer_connect); without it such a layout is refused */
 
 typedef struct gsm_ctx gsm_ctx;
 
@@ -161,6 +163,12 @@ const int32_t* gsm_result_steps(const gsm_ctx* ctx, int sid);
 /* bit 0: a sample hit the dwell-step cap (2^20; rates <= 0 hang the reference)
  * bit 1: the peer exchange timed out waiting for another rank (the histogram is partial) */
 uint64_t gsm_result_flags(const gsm_ctx* ctx, int sid);
+/* %globaltimer stamps (ns, this GPU's clock) the last block of the last run left behind:
+ * [0] it started finalising, [1] its partial histogram and arrival flags were posted to every peer,
+ * [2] every peer's flag had arrived, [3] results written.  [1] = [2] = [0] without a peer exchange.
+ * [2] - [1] on the rank that arrived last is the cost of the exchange itself; on the other ranks it
+ * also holds the time they were ahead (skew).  Returns GSM_ESTATE before the first run. */
+int gsm_result_timing(const gsm_ctx* ctx, int sid, uint64_t out_ns[4]);
 /* device time of the last run on the slot between its first and last enqueued operation, ms */
 float gsm_last_elapsed_ms(gsm_ctx* ctx, int sid);
 /* number of kernels this library launched on behalf of the context so far */
@@ -184,7 +192,17 @@ int gsm_comm_destroy(gsm_ctx* ctx);
  *   3. every rank: gsm_peer_connect(ctx, handles, rank, world)
  * Every rank must then issue the same sequence of gsm_run* calls per stream slot.  A rank whose
  * peer does not arrive within the timeout (default 20 s) reports flag bit 1 in gsm_result_flags.
- * Exclusive with gsm_comm_init. */
+ * Exclusive with gsm_comm_init.
+ * Forward progress: the last block of a launch WAITS inside the kernel for the other ranks'
+ * launches, so all ranks of an exchange must be able to execute at the same time.  One rank per
+ * GPU (the intended layout) guarantees that.  Ranks that share a GPU — several contexts of one
+ * process on one device, or several processes on one device — depend on the GPU running their
+ * kernels concurrently, which CUDA does not promise: gsm_peer_connect refuses such a layout
+ * (GSM_ESTATE) unless the context was created with GSM_PEER_SHARED_DEVICE, and even then only when
+ * co-resident ranks x stream slots fit the device's hardware queues (CUDA_DEVICE_MAX_CONNECTIONS,
+ * default 8) and CUDA_LAUNCH_BLOCKING is not set; ranks of different processes on one GPU then
+ * advance by the driver's time-slicing (or MPS) — live, but slow.  Under a kernel-serialising
+ * profiler (ncu) use one rank per GPU or the NCCL path (gsm_comm_init). */
 #define GSM_PEER_HANDLE_BYTES 128
 #define GSM_MAX_PEERS 8
 int gsm_peer_export(gsm_ctx* ctx, int world, int max_P, void* handle_out128);

@@ -333,6 +333,16 @@ class RefGpu:
         R = int(self.lib.refgpu_resample(self.h))
         return np.ctypeslib.as_array(self.lib.refgpu_hmcE(self.h, sid), shape=(N * R,)).copy()
 
+    def host_half(self, N, n, K, nb=200, left_pad=2, sid=0):
+        """seconds for K host halves of an evaluation (vector copy + boost::histogram + chi-square,
+        streamWorker.cpp:187-206) on the last hmcE; -> (seconds, chi2)"""
+        self.lib.refgpu_host_half.restype = C.c_double
+        self.lib.refgpu_host_half.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                              C.POINTER(C.c_float)]
+        c = C.c_float(0)
+        s = self.lib.refgpu_host_half(self.h, sid, N, nb, left_pad, n, K, C.byref(c))
+        return float(s), float(c.value)
+
     def time(self, n, args, K, sid=0) -> float:
         a = np.ascontiguousarray(args, np.float32)
         return float(self.lib.refgpu_time(self.h, n, _ptr(a, _f32p), sid, K))

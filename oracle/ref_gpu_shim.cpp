@@ -105,4 +105,15 @@ double refgpu_time(void* h, int n, const float* args, int sid, int K)
     return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 
+// the HOST half of one reference evaluation lives in ref_host_half.cpp (plain C++: nvcc's front end
+// does not take boost::histogram); this hands it the reference's own buffers
+double ref_host_half(const float* mcE, size_t count, const float* sg, size_t n_sg, int R, int fret_hist_num, int left_pad,
+                     int n_states, int K, float* chi2_out);
+double refgpu_host_half(void* h, int sid, int N, int fret_hist_num, int left_pad, int n_states, int K, float* chi2_out)
+{
+    RefGpu* r = (RefGpu*)h;
+    return ref_host_half(r->m->hmcE[sid], (size_t)N * r->m->reSampleTimes, r->sg.data(), r->sg.size(), r->m->reSampleTimes,
+                         fret_hist_num, left_pad, n_states, K, chi2_out);
+}
+
 }  // extern "C"

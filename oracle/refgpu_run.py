@@ -8,8 +8,8 @@ its own (its destructor resets the device) and writes what the checks need:
   x.npz: mcE[evals, N*R] float32 (the reference's hmcE after each evaluation; its Sobol
          states persist from one evaluation to the next, quirk Q8), R, N
   --time K additionally prints one JSON line with the reference's burst-samples/s through its own
-         API (set_params ... run_kernel + D2H + streamQuery; the host histogram of
-         streamWorker.cpp:187-206 is timed too, with numpy's bincount standing in for boost)
+         API (set_params ... run_kernel + D2H + streamQuery; the host histogram + chi-square of
+         streamWorker.cpp:187-206 is timed too, through the reference's vendored boost::histogram)
 """
 import argparse
 import json
@@ -38,6 +38,7 @@ def main():
     import oracle_py
     from gsmfretda_b200 import synth
 
+    STAGES = {}
     w = synth.workload(a.cfg, n_bursts=a.bursts, R=a.repeats)
     b = w.bursts()
     devnull = os.open(os.devnull, os.O_WRONLY)
@@ -47,6 +48,7 @@ def main():
         def stage(msg, t=[time.perf_counter()]):
             now = time.perf_counter()
             print("[refgpu_run] %s (+%.2f s)" % (msg, now - t[0]), file=sys.stderr, flush=True)
+            STAGES[msg] = round(now - t[0], 3)
             t[0] = now
         m = oracle_py.RefGpu(0, 1)
         stage("created")
@@ -62,17 +64,13 @@ def main():
         if a.time > 0:
             m.time(w.n_states, arg, 3)
             s = m.time(w.n_states, arg, a.time)
-            # the host-side part the reference does per evaluation (streamWorker.cpp:187-206)
-            e = out[-1]
-            t0 = time.perf_counter()
-            for _ in range(3):
-                z = e.astype(np.float64)
-                idx = (z[(z >= 0) & (z < 1)] * 200).astype(np.int64)
-                np.bincount(idx, minlength=200)
-            host_s = (time.perf_counter() - t0) / 3
+            # the host half the reference does per evaluation (streamWorker.cpp:187-206): its own
+            # boost::histogram (the vendored copy) + chi-square loop, compiled into libref_gpu.so
+            host_total, chi2 = m.host_half(b.n_bursts, w.n_states, 3)
+            host_s = host_total / 3
             line = {"impl": "reference class mc on the GPU (oracle/_ref/libref_gpu.so)", "bursts": b.n_bursts,
                     "repeats": R, "evals_timed": a.time, "kernel_plus_d2h_s_per_eval": s / a.time,
-                    "host_hist_s_per_eval": host_s,
+                    "host_hist_s_per_eval": host_s, "chi2": chi2, "stages_s": STAGES,
                     "burst_samples_per_s_kernel_d2h": b.n_bursts * R * a.time / s,
                     "burst_samples_per_s_with_host_hist": b.n_bursts * R / (s / a.time + host_s)}
     finally:

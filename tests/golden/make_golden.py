@@ -78,6 +78,22 @@ def main():
             ph_count=b.ph_count, T=b.T, burst_ad=b.burst_ad, burst_dd=b.burst_dd, SgDivSr=b.SgDivSr,
             clk_p=b.clk_p, bg_ad_rate=b.bg_ad_rate, bg_dd_rate=b.bg_dd_rate, n=n, args=args, R=8,
             seed=909, epoch=9, ref_E=E, ref_v=v, ref_K=K, ref_P_i2j=Pij, ref_p=p, ref_mcE=mcE)
+    # n = 5, 6 (the top of the reference's own test matrix, tests/gen_rand_tests.cpp:79-82) and
+    # n = 8 (the top of get_max_conversion_capacity's default range), full K matrices
+    for n, bg, seed in ((5, 0.0, 515), (6, 1.0, 616), (8, 0.0, 818)):
+        rng = np.random.default_rng(9000 + n)
+        E = np.linspace(0.08, 0.92, n)
+        k = np.exp(rng.uniform(np.log(150.0), np.log(4000.0), size=n * n - n))
+        args = synth.pack_args(E, k, rng.uniform(1.0, 3.0, size=n))
+        b = synth.make_bursts(160, E, seed=seed, bg_ad_rate=1200.0 * bg, bg_dd_rate=2000.0 * bg)
+        ok, Ee, v, K, Pij, pp = R.params(n, args)
+        assert ok
+        mcE = R.mc_kernel(b, n, args, 4, seed, n)
+        np.savez_compressed(
+            os.path.join(HERE, f"n{n}_fullK{'_bg' if bg else ''}_p0.npz"), start=b.start, stop=b.stop, istart=b.istart,
+            ph_count=b.ph_count, T=b.T, burst_ad=b.burst_ad, burst_dd=b.burst_dd, SgDivSr=b.SgDivSr,
+            clk_p=b.clk_p, bg_ad_rate=b.bg_ad_rate, bg_dd_rate=b.bg_dd_rate, n=n, args=args, R=4,
+            seed=seed, epoch=n, ref_E=Ee, ref_v=v, ref_K=K, ref_P_i2j=Pij, ref_p=pp, ref_mcE=mcE)
     print("golden vectors written to", HERE)
 
 

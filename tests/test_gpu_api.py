@@ -2,6 +2,8 @@
 entry points, edge cases, error behaviour, and full-size property checks."""
 import ctypes as C
 
+import os
+
 import numpy as np
 import pytest
 
@@ -227,8 +229,9 @@ def test_step_cap_flags_nonpositive_rates(gsm):
 @pytest.mark.parametrize("cfg", [2, 3, 5])
 def test_full_size_properties(gsm, oracle, cfg):
     """BASELINE.json sizes (config 5 at 1e6 bursts: the generator, not the GPU, is the limit):
-    histogram mass, determinism, epoch sensitivity, additivity over burst ranges, and a
-    sampled bit-exact check of the first 2000 bursts against the oracle."""
+    histogram mass, determinism, epoch sensitivity, additivity over burst ranges, a bit-exact
+    check of the first 2000 bursts sample by sample, and the whole histogram + chi-square of the
+    full-size evaluation bit for bit against the oracle."""
     w = synth.workload(cfg, n_bursts=1_000_000 if cfg == 5 else None)
     b = w.bursts()
     B, R, n = b.n_bursts, w.R, w.n_states
@@ -247,6 +250,11 @@ def test_full_size_properties(gsm, oracle, cfg):
         _, ha = mc.evaluate(n, w.args[0], sid=0, N=2000, epoch=5)
         o = oracle.eval(b, n, w.args[0], R, 77, 5, 0, 2000)
         assert np.array_equal(ha, oracle.hist(o["mcE"], NB))
+    # the WHOLE histogram and chi-square at full size, bit for bit, against the oracle on all host cores
+    co, ho = oracle.eval_chi2(b, n, w.args[0], R, 77, 5, oracle.observed_hist(b, NB), NB, LEFT_PAD,
+                              nthreads=len(os.sched_getaffinity(0)))
+    assert np.array_equal(h1, ho), int((h1 != ho).sum())
+    assert np.float32(c1).view(np.uint32) == np.float32(co).view(np.uint32)
     # additivity: two contexts holding the two halves with global burst ids sum to the whole
     half = B // 2
     hs = np.zeros(NB + 2, np.uint64)

@@ -111,6 +111,29 @@ def test_batched_p_ga_is_one_launch_per_batch_and_the_same_numbers(world, extra)
         srv.close()
 
 
+@pytest.mark.parametrize("batch", [1, 4])
+def test_one_node_spanning_gpus_matches_the_oracle(world, gsm, batch):
+    """`gSMFRETda -g a,b`: ONE node, one set of REQ clients, the dataset split over the listed GPUs
+    inside the process (multi-GPU `mc`, fused peer exchange) — what replaces one node per GPU
+    (/root/reference/src/call_main.cpp:195-227) when it is the dataset that is large.  Same wire
+    conversation, same numbers as the oracle over the whole dataset, single vectors and batches."""
+    ndev = gsm.load().gsm_device_count()
+    gpus, extra = ("0,1", ()) if ndev >= 2 else ("0,0", ("--oversubscribe",))
+    best = float(np.median([c for _, c in world["want"]]))
+    srv = ParamServer(2, world["vecs"], bestfv=best, batch=batch)
+    try:
+        r = run_node(srv, os.path.join(H5, "from_bin.h5"), "-g", gpus, *extra, streams=2)
+        assert "GPUs: " + gpus.replace(",", " ") in r.stdout
+        assert sorted(srv.results) == list(range(len(world["vecs"])))
+        for i, (h, c) in enumerate(world["want"]):
+            assert np.float32(srv.results[i]["e"]) == np.float32(c), (i, srv.results[i]["e"], c)
+            if srv.results[i]["hist"]:
+                assert np.array_equal(np.array(srv.results[i]["shist"], np.float32), h[:NB].astype(np.float32) / np.float32(R))
+        assert any(v["hist"] for v in srv.results.values())
+    finally:
+        srv.close()
+
+
 def test_a_refused_vector_is_reported_not_evaluated(world):
     """A vector the library refuses (here: the server announces 1 state, genMatK's empty rate list,
     eigenhelper.cpp:5-8) launches nothing: chi-square +inf, no histogram — never the numbers of the

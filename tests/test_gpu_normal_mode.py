@@ -225,3 +225,36 @@ def test_normal_btpe_window(gsm, oracle):
     assert abs(a["sum_ai"].mean() - r["sum_ai"].mean()) < 6 * se
     D, p = ks(a["mcE"], r["mcE"])
     assert p > 0.01, (D, p)
+
+
+def test_normal_photon_rich_window_small_p(gsm):
+    """Windows of 2e4 photons with p = 1e-3 (n*p = 20: still the FP32 inversion, whose start value
+    is exp(n log(1-p)) — an absolute error in the logarithm is multiplied by n there).  The acceptor
+    counts of the normal mode must follow the replay mode's distribution: mean within 4 standard
+    errors, count histograms homogeneous, KS on E."""
+    rng = np.random.default_rng(8)
+    B, ph = 2000, 20000
+    start = (np.arange(B, dtype=np.int64) * 4000000 + 1000)
+    dur = np.full(B, 2000000, np.int64)
+    t = np.sort(rng.integers(1, 1999999, size=(B, ph)), axis=1) + start[:, None]
+    ad = t.reshape(-1)
+    b = synth.Bursts(start=start, stop=start + dur, istart=np.arange(B, dtype=np.int64) * ph,
+                     ph_count=np.full(B, ph, np.int32), T=(dur * 1.25e-8).astype(np.float32),
+                     burst_ad=ad, burst_dd=np.zeros_like(ad), SgDivSr=np.full(B, 0.001, np.float32))
+    args = synth.pack_args([0.001, 0.001], [1e-3, 1e-3], [1.0, 1.0])
+    a = run(gsm, b, 2, args, 32, 21, 1, gsm.GSM_MODE_NORMAL)
+    r = run(gsm, b, 2, args, 32, 22, 1, gsm.GSM_MODE_REPLAY)
+    assert a["flags"] == 0 and r["flags"] == 0
+    m = r["sum_ai"].mean()
+    assert 15 < m < 25, m
+    se = np.sqrt(a["sum_ai"].var() / a["sum_ai"].size + r["sum_ai"].var() / r["sum_ai"].size)
+    assert abs(a["sum_ai"].mean() - m) < 4 * se, (a["sum_ai"].mean(), m, se)
+    from scipy import stats
+    top = int(max(a["sum_ai"].max(), r["sum_ai"].max())) + 1
+    ha = np.bincount(a["sum_ai"], minlength=top).astype(np.float64)
+    hr = np.bincount(r["sum_ai"], minlength=top).astype(np.float64)
+    keep = (ha + hr) >= 20
+    st = float((((ha - hr) ** 2)[keep] / (ha + hr)[keep]).sum())
+    assert stats.chi2.sf(st, int(keep.sum()) - 1) > 0.001, st
+    D, p = ks(a["mcE"], r["mcE"])
+    assert p > 0.001, (D, p)

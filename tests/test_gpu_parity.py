@@ -69,3 +69,44 @@ def test_raw64_layout_bit_exact(gsm, oracle, cfg):
 def test_partial_range(gsm, oracle):
     w = synth.workload(3, n_bursts=1000, R=16)
     check(gsm, oracle, w.bursts(), w.n_states, w.args[0], 16, N=333)
+
+
+def many_state_case(n, bg, nb=1500, seed=9100):
+    """n states, full K matrix (every off-diagonal rate its own), optionally with background."""
+    rng = np.random.default_rng(seed + n)
+    E = np.linspace(0.08, 0.92, n)
+    k = np.exp(rng.uniform(np.log(150.0), np.log(4000.0), size=n * n - n))
+    args = synth.pack_args(E, k, rng.uniform(1.0, 3.0, size=n))
+    b = synth.make_bursts(nb, E, seed=seed + 7 * n, bg_ad_rate=1200.0 * bg, bg_dd_rate=2000.0 * bg)
+    return b, args
+
+
+@pytest.mark.parametrize("n,bg", [(5, 0), (5, 1), (6, 0), (6, 1), (7, 0), (8, 0), (8, 1)])
+def test_many_states_bit_exact(gsm, oracle, n, bg):
+    """n = 5, 6 are the top of the reference's own test matrix (/root/reference/tests/gen_rand_tests.cpp:79-82);
+    n = 8 is the top of get_max_conversion_capacity's range (/root/reference/src/mc.cu:402-438)."""
+    b, args = many_state_case(n, bg)
+    for kw in ({}, dict(no_index=True)):
+        g = check(gsm, oracle, b, n, args, 8, seed=31 + n, epoch=n, **kw)
+        assert g["packed"]
+
+
+def test_many_states_batch_bit_exact(gsm, oracle):
+    """A batch of 6-state vectors in one launch equals the oracle vector by vector."""
+    n = 6
+    b, a0 = many_state_case(n, 1, nb=800)
+    rng = np.random.default_rng(5)
+    vecs = np.stack([a0 * np.concatenate([np.ones(n), rng.uniform(0.5, 2.0, n * n - n), np.ones(n)]).astype(np.float32)
+                     for _ in range(5)])
+    with gsm.Mc(0, 1) as mc:
+        mc.set_reSampleTimes(4); mc.set_seed(99); mc.set_hist(NB, LEFT_PAD)
+        mc.init_bursts(b)
+        mc.set_epoch(0, 40)
+        mc.run_batch(b.n_bursts, 0, n, vecs)
+        mc.sync(0)
+        chi = mc.chi2v(0)
+        ohist = oracle.observed_hist(b, NB)
+        for p in range(5):
+            c, h = oracle.eval_chi2(b, n, vecs[p], 4, 99, 40 + p, ohist, NB, LEFT_PAD)
+            assert np.array_equal(mc.hist(0, p), h)
+            assert np.float32(chi[p]).view(np.uint32) == np.float32(c).view(np.uint32)

@@ -28,8 +28,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def _connected(gsm, b, world, R, seed, max_P=1, streams=1, mode=0):
     parts = sharding.split_bursts(b.ph_count, world)
     mcs = []
-    for (b0, b1) in parts:
-        mc = gsm.Mc(0, streams)
+    ndev = max(1, gsm.load().gsm_device_count())
+    for r, (b0, b1) in enumerate(parts):
+        # rank r on GPU r % #GPUs: real peer memory over NVLink where the box has several GPUs; ranks
+        # that have to share a GPU say so (GSM_PEER_SHARED_DEVICE; conftest gives them hardware queues)
+        mc = gsm.Mc(r % ndev, streams, peer_shared_device=world > ndev)
         mc.set_reSampleTimes(R); mc.set_seed(seed); mc.set_hist(NB, LEFT_PAD); mc.set_mode(mode)
         mc.init_bursts(b.slice(b0, b1), g_offset=b0)
         mcs.append(mc)
@@ -123,6 +126,44 @@ def test_peer_timeout_is_reported_not_hung(gsm):
             mc.close()
 
 
+def test_ranks_sharing_a_gpu_are_refused_without_the_flag(gsm):
+    """The in-kernel wait needs all ranks running at once: two ranks on one GPU are only accepted
+    from a caller that vouches for it, and never with more (ranks x slots) than hardware queues."""
+    w = synth.workload(2, n_bursts=200, R=4)
+    b = w.bursts()
+
+    def pair(streams, **kw):
+        mcs = [gsm.Mc(0, streams, **kw) for _ in range(2)]
+        for r, mc in enumerate(mcs):
+            mc.set_reSampleTimes(4); mc.init_bursts(b.slice(100 * r, 100 * r + 100), g_offset=100 * r)
+        return mcs, [mc.peer_export(2, 1) for mc in mcs]
+
+    mcs, hs = pair(1)
+    try:
+        with pytest.raises(RuntimeError, match="share GPU"):
+            mcs[0].peer_connect(hs, 0, 2)
+    finally:
+        for mc in mcs:
+            mc.close()
+    queues = int(os.environ.get("CUDA_DEVICE_MAX_CONNECTIONS", "8"))
+    mcs, hs = pair(queues, peer_shared_device=True)      # 2 ranks x `queues` slots: twice too many
+    try:
+        with pytest.raises(RuntimeError, match="hardware queues"):
+            mcs[0].peer_connect(hs, 0, 2)
+    finally:
+        for mc in mcs:
+            mc.close()
+    mcs, hs = pair(1, peer_shared_device=True)
+    try:
+        for r, mc in enumerate(mcs):
+            mc.peer_connect(hs, r, 2)
+        with pytest.raises(RuntimeError, match="disconnect first"):   # peers have the block mapped
+            mcs[0].peer_export(2, 1)
+    finally:
+        for mc in mcs:
+            mc.close()
+
+
 def test_peer_api_errors(gsm):
     w = synth.workload(2, n_bursts=100, R=4)
     b = w.bursts()
@@ -148,7 +189,8 @@ rank, world, d = int(sys.argv[1]), int(sys.argv[2]), sys.argv[3]
 w = synth.workload(2, n_bursts=4000, R=8)
 b = w.bursts()
 b0, b1 = sharding.split_bursts(b.ph_count, world)[rank]
-mc = capi.Mc(rank % capi.load().gsm_device_count(), 1)   # one GPU per rank where the box has them
+ndev = capi.load().gsm_device_count()
+mc = capi.Mc(rank % ndev, 1, peer_shared_device=world > ndev)   # one GPU per rank where the box has them
 mc.set_reSampleTimes(w.R); mc.set_seed(12); mc.set_hist(200, 2)
 mc.init_bursts(b.slice(b0, b1), g_offset=b0)
 open(os.path.join(d, f"h{{rank}}.tmp"), "wb").write(mc.peer_export(world, 1))

@@ -141,12 +141,15 @@ def test_split_node_plans_like_sharding_py(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("parts", [1, 2, 5])
-def test_split_node_matches_oracle(oracle, tmp_path, parts):
-    """One dataset cut into `parts` burst ranges, one context each (sharing the GPUs there are),
-    histogram exchange fused into the evaluation kernel, driven from C++: the global histogram and
-    chi-square equal the oracle's over the whole dataset, whatever the number of parts."""
+@pytest.mark.parametrize("parts,over", [(1, False), (2, True), (5, True), (5, False)])
+def test_split_node_matches_oracle(oracle, gsm, tmp_path, parts, over):
+    """One dataset cut into `parts` burst ranges behind ONE multi-GPU `mc` (host/mc.hpp), histogram
+    exchange fused into the evaluation kernel, driven from C++: the global histogram and chi-square
+    equal the oracle's over the whole dataset, whatever the number of parts.  Parts beyond the
+    number of GPUs are merged unless --oversubscribe keeps them apart on shared GPUs."""
     build()
+    ngpu = gsm.load().gsm_device_count()
+    used = parts if (over or parts <= ngpu) else ngpu
     exe = os.path.join(HOST, "split_node")
     w = synth.workload(5, n_bursts=1500, R=4)
     b = w.bursts()
@@ -155,10 +158,10 @@ def test_split_node_matches_oracle(oracle, tmp_path, parts):
     with open(tmp_path / "p.txt", "w") as f:
         for n, a in vecs:
             f.write(f"{n} " + " ".join(repr(float(x)) for x in a) + "\n")
-    r = subprocess.run([exe, str(tmp_path / "b.bin"), str(tmp_path / "p.txt"), str(tmp_path / "o.txt"), str(parts), "4", "42"],
-                       capture_output=True, text=True, timeout=180)
+    r = subprocess.run([exe, str(tmp_path / "b.bin"), str(tmp_path / "p.txt"), str(tmp_path / "o.txt"), str(parts), "4", "42"]
+                       + (["--oversubscribe"] if over else []), capture_output=True, text=True, timeout=180)
     assert r.returncode == 0, (r.stdout, r.stderr)
-    assert f"split into {parts} parts" in r.stdout
+    assert f"split into {used} part(s) ({parts} asked)" in r.stdout
     rows = [l.split() for l in open(tmp_path / "o.txt") if l.strip()]
     assert len(rows) == len(vecs)
     ohist = oracle.observed_hist(b, NB)
