@@ -28,6 +28,22 @@ constexpr int kChunkMax = PDA_CHUNK_MAX;  // most consecutive samples a warp dra
 constexpr int kMaxBins = 1024;          // nb + 2 <= kMaxBins
 constexpr uint32_t kStepCap = 1u << 20; // guards the GPU against rates <= 0 (a hang in the reference)
 
+// Replay mode defers the FP64 binomial draws: the walk of a lane only RECORDS them (one 16-byte
+// entry per draw in a lane-private queue in shared memory) and the warp works the queues off
+// together every few trips — the exp/log start values of all recorded draws packed 32 to a
+// warp-instruction, then the inversion loops of all lanes merged into one loop.  The draws of a
+// sample stay in order on the sample's own xor128 stream, so the results are the same bits.
+#ifndef PDA_FIFO_D
+#define PDA_FIFO_D 8
+#endif
+#ifndef PDA_FETCH_TH
+#define PDA_FETCH_TH 12
+#endif
+constexpr int kFifoD = PDA_FIFO_D;       // entries per lane (a trip adds at most 3: start, draw, end)
+constexpr int kFetchTh = PDA_FETCH_TH;   // lanes that must be waiting before the merged loop stops to fetch
+constexpr uint32_t kEntDraw = 0u, kEntStart = 1u, kEntEnd = 2u;
+static_assert(kFifoD >= 4 && kFifoD <= 16, "two kind bits per entry live in one 32-bit register");
+
 // parameter vector staged in shared memory, with the per-state terms hoisted
 struct SmemParams {
     int n;
@@ -244,7 +260,8 @@ __device__ __forceinline__ void lane_begin(Lane& L, const SmemParams& sp, const 
         L.xs.s0 = xs.x; L.xs.s1 = xs.y; L.xs.s2 = xs.z; L.xs.s3 = xs.w;
     }
     // replay mode: the xor128 stream of the sample is seeded from its step-0 block (lane_step)
-    L.F = 0.0f; L.acc = 0.0f; L.spent = 0.0f;
+    L.F = 0.0f; L.spent = 0.0f;
+    if (kMode != kModeReplay) L.acc = 0.0f;   // replay: the queue's start entry resets it (the consumer owns acc and xs)
     L.fb = (float)L.start;
     L.first = 0;
     L.step = 0;
@@ -259,9 +276,12 @@ __device__ __forceinline__ void lane_save_reference(const Lane& L, const EvalArg
 }
 
 // one dwell window (one trip of the reference's while loop, mc.cu:117-191)
+// Replay mode returns the binomial draw of the window instead of taking it: has_draw, (draw_n, draw_p),
+// and at step 0 the seed of the sample's xor128 stream.
 template <int kLayout, bool kBg, int kMode>
 __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const EvalArgs& a, uint32_t epoch,
-                                          const double2* __restrict__ ltab, const double* __restrict__ rcp)
+                                          const double2* __restrict__ ltab, const double* __restrict__ rcp,
+                                          uint32_t& seed_out, bool& has_draw, int& draw_n, float& draw_p)
 {
     constexpr bool kFast = kMode == kModeNormal;
     constexpr bool kSobol = kMode == kModeReference;
@@ -288,7 +308,7 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
         if (kFast) iw = (w.x & 0xffu) | ((w.y & 0xffu) << 8) | ((w.z & 0xffu) << 16) | (w.w << 24);
         else if (!kSobol) {
             iw = ((w.x & 0xffu) << 24) | ((w.y & 0xffu) << 16) | ((w.z & 0xffu) << 8) | 0x80u;
-            L.xs.seed((uint64_t)w.w);
+            seed_out = w.w;
         }
         L.si = pick(sp.cumP, n, u01(iw));
     }
@@ -383,10 +403,16 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
             if (kSobol) w.z = (uint32_t)(sobol_next(L) >> 32);
             const float rd = det_norm_icdf(w.z) * sp.v[si] + sp.rootE[si];
             const float de = 1.0f / (1.0f + det_pow6f(rd / kR0));
-            ai = (int)binomial(L.xs, (int)f_i, (double)de, ltab);
+            if (kMode == kModeReplay) {
+                has_draw = true;
+                draw_n = (int)f_i;
+                draw_p = de;
+            } else {
+                ai = (int)binomial(L.xs, (int)f_i, (double)de, ltab);
+            }
         }
     }
-    L.acc += (float)ai;
+    if (kMode != kModeReplay) L.acc += (float)ai;
     L.si = sj;
     L.step++;
 }
@@ -587,6 +613,13 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
     const int nbp = a.nb + 2;
     SmemParams& sp = s_params[wid];
     unsigned int* hist = s_hist_all + wid * nbp;
+    // replay mode: the warp's draw queues, entry e of lane l at [e * 32 + l] (conflict-free), and
+    // the list of the entries that are draws (filled in arrival order, read 32 at a time)
+    constexpr bool kDefer = kMode == kModeReplay;
+    uint4* fifo = reinterpret_cast<uint4*>(s_hist_all + ((kWarps * nbp + 3) & ~3)) + wid * (kFifoD * 32);
+    unsigned short* drawref = reinterpret_cast<unsigned short*>(
+                                  reinterpret_cast<uint4*>(s_hist_all + ((kWarps * nbp + 3) & ~3)) + kWarps * (kFifoD * 32)) +
+                              wid * (kFifoD * 32);
 
     const int64_t per_p = a.N * (int64_t)a.R;  // samples per parameter vector
     const unsigned long long chunks_per_p = (unsigned long long)((per_p + a.chunk - 1) >> a.chunk_log2);
@@ -611,8 +644,14 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
 
     Lane L;
     bool active = false;
+    // queue state (replay mode): entries of this lane, their kinds (2 bits each), draws of the warp
+    int q_cnt = 0;
+    uint32_t q_kinds = 0u;
+    int w_draws = 0;
+    const bool keep_samples = a.mcE || a.sum_ai || a.n_steps;
 
     for (;;) {
+        bool drain = false;
         // ---- hand samples to idle lanes -------------------------------------------------
         for (;;) {
             const unsigned need = __ballot_sync(0xffffffffu, !active);
@@ -638,10 +677,13 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
                 const int p = small ? (int)((uint32_t)item / (uint32_t)chunks_per_p) : (int)(item / chunks_per_p);
                 const int cur_p = wc.cur_p;
                 if (p != cur_p) {
-                    if (need != 0xffffffffu) {   // park the chunk until every lane has drained
+                    // the samples still in the queues belong to the histogram of the previous vector
+                    const bool queued = kDefer && __any_sync(0xffffffffu, q_cnt > 0);
+                    if (need != 0xffffffffu || queued) {   // park the chunk until every lane has drained
                         __syncwarp();
                         if (lane == 0) { wc.have_pending = 1; wc.pend_item = item; }
                         __syncwarp();
+                        drain = queued;
                         break;
                     }
                     // all lanes idle: switch vector
@@ -707,27 +749,152 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
                 active = false;
             }
         }
-        if (__ballot_sync(0xffffffffu, active) == 0u) {
+        const bool none_active = __ballot_sync(0xffffffffu, active) == 0u;
+
+        // ---- replay mode: work the draw queues off -----------------------------------------
+        // when a queue could overflow in the coming trip, before the histogram changes hands, and
+        // when the warp has nothing else left
+        if (kDefer && (drain || none_active || __any_sync(0xffffffffu, q_cnt > kFifoD - 3)) &&
+            __any_sync(0xffffffffu, q_cnt > 0)) {
+            // pass 1: q^n = exp(n log(1 - p)) of every recorded draw that the inversion will take,
+            // the draws of all lanes dealt 32 at a time (no order among them: nothing is drawn yet)
+            for (int k = lane; k < w_draws; k += 32) {
+                uint4* ent = fifo + drawref[k];
+                const int n = (int)ent->x;
+                const double p = (double)__uint_as_float(ent->y);
+                const bool no_trials = n <= 0 && n >= -64 && p > 0.0 && p < 1.0;
+                const double pp = !(p <= 0.5) ? 1.0 - p : p;
+                if (!no_trials && pp * (double)n <= 30.0) {
+                    const double qn = det_exp((double)n * det_log(1.0 - pp, s_logtab));
+                    ent->z = (uint32_t)__double2loint(qn);
+                    ent->w = (uint32_t)__double2hiint(qn);
+                }
+            }
+            __syncwarp();
+            // pass 2: every lane walks its own queue in order on the sample's xor128 stream; the
+            // inversion loops (role of rk_binomial_inversion, binom.cuh:135-169) of the lanes are ONE
+            // loop, a lane that finishes a draw waits until enough others have to fetch the next
+            int rd = 0;
+            bool have = false, mir = false;
+            int n = 0, X = 0, bound = 0;
+            double pp = 0.0, q = 1.0, qn = 1.0, px = 1.0, U = 0.0, dX = 0.0, dn1 = 1.0;
+            for (;;) {
+                const unsigned idle = __ballot_sync(0xffffffffu, !have && rd < q_cnt);
+                const unsigned busy = __ballot_sync(0xffffffffu, have);
+                if ((idle | busy) == 0u) break;
+                if (idle != 0u && (busy == 0u || __popc(idle) >= kFetchTh)) {
+                    if (!have) {
+                        while (rd < q_cnt) {
+                            const uint4 ent = fifo[rd * 32 + lane];
+                            const uint32_t kind = (q_kinds >> (2 * rd)) & 3u;
+                            ++rd;
+                            if (kind == kEntStart) {
+                                L.xs.seed((uint64_t)ent.y);   // role of setup_kernel's rk_seed, gen_rand.cuh:19-21
+                                L.acc = 0.0f;
+                            } else if (kind == kEntEnd) {
+                                // IEEE division in both modes: E takes few distinct values (small integer
+                                // counts), so a 1-ulp difference would move whole atoms of the distribution.
+                                // 0 / F = +0 is spelled out: a zero numerator sends the division through its slow path.
+                                const float F = __uint_as_float(ent.y);
+                                const float e = (F > 0.0f && L.acc != 0.0f) ? __fdiv_rn(L.acc, F) : 0.0f;
+                                if (keep_samples) {
+                                    const size_t oi = ((size_t)ent.w << 32) | (size_t)ent.z;
+                                    if (a.mcE) a.mcE[oi] = e;
+                                    if (a.sum_ai) a.sum_ai[oi] = (long long)L.acc;   // integer-valued, exact below 2^24
+                                    if (a.n_steps) a.n_steps[oi] = (int32_t)ent.x;
+                                }
+                                const int bin = hist_index(e, a.nb);
+                                const unsigned fm = __activemask();
+                                const unsigned peers = __match_any_sync(fm, bin);
+                                if (lane == __ffs(peers) - 1) atomicAdd(&hist[bin], (unsigned)__popc(peers));
+                            } else {
+                                // the cases of binomial() (pda_device.cuh), in its order
+                                n = (int)ent.x;
+                                const double p = (double)__uint_as_float(ent.y);
+                                if (n <= 0 && n >= -64 && p > 0.0 && p < 1.0) {
+                                    L.xs.next();
+                                    L.xs.next();
+                                    L.acc += (float)(p <= 0.5 ? 0 : n);
+                                    continue;
+                                }
+                                mir = !(p <= 0.5);
+                                pp = mir ? 1.0 - p : p;
+                                if (pp * (double)n <= 30.0) {
+                                    q = 1.0 - pp;
+                                    qn = __hiloint2double((int)ent.w, (int)ent.z);
+                                    bound = n;
+                                    if (n < 1 || n > 10) {
+                                        const double np = (double)n * pp;
+                                        double bd = np + 10.0 * __dsqrt_rn(np * q + 1.0);
+                                        if (!(bd <= (double)n)) bd = (double)n;
+                                        bound = (int)bd;
+                                    }
+                                    X = 0;
+                                    dX = 0.0;
+                                    dn1 = (double)n + 1.0;
+                                    px = qn;
+                                    U = L.xs.next_double();
+                                    have = true;
+                                    break;
+                                }
+                                Xor128 t = L.xs;
+                                const long long Xb = binomial_btpe(t, n, pp);
+                                L.xs = t;
+                                L.acc += (float)(int)(mir ? (long long)n - Xb : Xb);
+                            }
+                        }
+                    }
+                }
+                if (have) {
+                    if (U > px) {
+                        X++;
+                        dX += 1.0;
+                        if (X > bound) {
+                            X = 0;
+                            dX = 0.0;
+                            px = qn;
+                            U = L.xs.next_double();
+                        } else {
+                            U -= px;
+                            px = ((dn1 - dX) * pp * px) / (dX * q);
+                        }
+                    } else {
+                        L.acc += (float)(mir ? n - X : X);
+                        have = false;
+                    }
+                }
+            }
+            q_cnt = 0;
+            q_kinds = 0u;
+            w_draws = 0;
+            __syncwarp();
+        }
+        if (none_active) {
             if (wc.exhausted && !wc.have_pending) break;
             continue;
         }
 
         // ---- one dwell window for every active lane -------------------------------------
+        bool fin = false, has_draw = false;
+        const bool first_step = active && L.step == 0u;
+        uint32_t seed = 0u;
+        int draw_n = 0;
+        float draw_p = 0.0f;
         if (active) {
-            lane_step<kLayout, kBg, kMode>(L, sp, a, wc.epoch, s_logtab, s_rcp);
-            bool fin = !(L.T > L.spent);
+            lane_step<kLayout, kBg, kMode>(L, sp, a, wc.epoch, s_logtab, s_rcp, seed, has_draw, draw_n, draw_p);
+            fin = !(L.T > L.spent);
             if (!fin && L.step >= kStepCap) {
                 atomicOr(a.counters + 2, 1ull);
                 fin = true;
             }
-            if (fin) {
+            if (fin && !kDefer) {
                 if (kMode == kModeReference) lane_save_reference(L, a);
                 // IEEE division in both modes: E takes few distinct values (small integer
                 // counts), so a 1-ulp difference would move whole atoms of the distribution.
                 // 0 / F = +0 is spelled out: a zero numerator (no acceptor photon drawn — a
                 // large share of the samples) sends the division through its slow path.
                 const float e = (L.F > 0.0f && L.acc != 0.0f) ? __fdiv_rn(L.acc, L.F) : 0.0f;
-                if (a.mcE || a.sum_ai || a.n_steps) {
+                if (keep_samples) {
                     const size_t oi = (size_t)wc.cur_p * (size_t)per_p + (size_t)L.bl * (size_t)a.R + L.rep;
                     if (a.mcE) a.mcE[oi] = e;
                     if (a.sum_ai) a.sum_ai[oi] = (long long)L.acc;   // integer-valued, exact below 2^24
@@ -739,10 +906,34 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
                 const unsigned fm = __activemask();
                 const unsigned peers = __match_any_sync(fm, bin);
                 if (lane == __ffs(peers) - 1) atomicAdd(&hist[bin], (unsigned)__popc(peers));
-                active = false;
             }
+            if (fin) active = false;
         }
         __syncwarp();
+        if (kDefer) {
+            // record what the window left to do, in the order the sample needs it
+            if (first_step) {
+                fifo[q_cnt * 32 + lane].y = seed;
+                q_kinds |= kEntStart << (2 * q_cnt);
+                ++q_cnt;
+            }
+            const unsigned dm = __ballot_sync(0xffffffffu, has_draw);
+            if (has_draw) {
+                const int at = q_cnt * 32 + lane;
+                fifo[at].x = (uint32_t)draw_n;
+                fifo[at].y = __float_as_uint(draw_p);
+                drawref[w_draws + __popc(dm & lt_mask)] = (unsigned short)at;
+                ++q_cnt;                         // kEntDraw = 0: no kind bits to set
+            }
+            w_draws += __popc(dm);
+            if (fin) {
+                const size_t oi = (size_t)wc.cur_p * (size_t)per_p + (size_t)L.bl * (size_t)a.R + L.rep;
+                fifo[q_cnt * 32 + lane] = make_uint4(L.step, __float_as_uint(L.F), (uint32_t)oi, (uint32_t)((unsigned long long)oi >> 32));
+                q_kinds |= kEntEnd << (2 * q_cnt);
+                ++q_cnt;
+            }
+            __syncwarp();
+        }
     }
     const int cur_p = wc.cur_p;
 
@@ -788,18 +979,27 @@ template <int kLayout, bool kBg, int kMode>
 static int resident_blocks(size_t dyn)
 {
     int nb = 0;
+    if (dyn > 48 * 1024)
+        cudaFuncSetAttribute(pda_eval_kernel<kLayout, kBg, kMode>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, pda_eval_kernel<kLayout, kBg, kMode>, kBlock, dyn);
     return nb < 1 ? 1 : nb;
 }
 
-static inline size_t eval_dyn_smem(int nb) { return (size_t)(kBlock / 32) * (size_t)(nb + 2) * sizeof(unsigned int); }
+// per-warp histograms, and in replay mode the draw queues (16 B entries) and the list of draws (2 B)
+template <int kMode>
+static inline size_t eval_dyn_smem(int nb)
+{
+    const size_t hist_words = ((size_t)(kBlock / 32) * (size_t)(nb + 2) + 3) & ~(size_t)3;
+    const size_t queues = kMode == kModeReplay ? (size_t)(kBlock / 32) * kFifoD * 32 * (16 + 2) : 0;
+    return hist_words * sizeof(unsigned int) + queues;
+}
 
 template <int kMode>
 static LaunchCfg eval_launch_cfg_t(int device, int layout, bool with_bg, int nb)
 {
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-    const size_t dyn = eval_dyn_smem(nb);
+    const size_t dyn = eval_dyn_smem<kMode>(nb);
     int per;
     if (layout == 0) per = with_bg ? resident_blocks<0, true, kMode>(dyn) : resident_blocks<0, false, kMode>(dyn);
     else if (layout == 1) per = with_bg ? resident_blocks<1, true, kMode>(dyn) : resident_blocks<1, false, kMode>(dyn);
@@ -834,7 +1034,7 @@ static cudaError_t launch_eval_t(const EvalArgs& a_in, int layout, bool with_bg,
     if (a_in.nb + 2 > kMaxBins) return cudaErrorInvalidValue;
     EvalArgs a = a_in;
     shape_launch(a, cfg);
-    const size_t dyn = eval_dyn_smem(a.nb);
+    const size_t dyn = eval_dyn_smem<kMode>(a.nb);
 #define PDA_LAUNCH(LAY, BG) pda_eval_kernel<LAY, BG, kMode><<<cfg.grid, cfg.block, dyn, s>>>(a)
     if (layout == 0) { if (with_bg) PDA_LAUNCH(0, true); else PDA_LAUNCH(0, false); }
     else if (layout == 1) { if (with_bg) PDA_LAUNCH(1, true); else PDA_LAUNCH(1, false); }
