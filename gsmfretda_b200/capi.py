@@ -69,6 +69,7 @@ SIGNATURES = {
     "gsm_set_epoch": (C.c_int, [_ctx, C.c_int, C.c_uint32]),
     "gsm_run": (C.c_int, [_ctx, C.c_int, C.c_int]),
     "gsm_run_batch": (C.c_int, [_ctx, C.c_int, C.c_int, C.c_int, C.c_int, _f32p]),
+    "gsm_run_coalesced": (C.c_int, [_ctx, C.c_int, C.c_int, C.c_int, C.c_int, _f32p, _i32p]),
     "gsm_run_resident": (C.c_int, [_ctx, C.c_int, C.c_int]),
     "gsm_query": (C.c_int, [_ctx, C.c_int]),
     "gsm_sync": (C.c_int, [_ctx, C.c_int]),
@@ -263,6 +264,14 @@ class Mc:
         a = np.ascontiguousarray(args2d, dtype=np.float32)
         assert a.ndim == 2 and a.shape[1] == n * n + n
         self._ck(self.lib.gsm_run_batch(self._h, N, sid, n, a.shape[0], _p(a, _f32p)))
+
+    def run_coalesced(self, N: int, carrier_sid: int, n: int, args2d, member_sids):
+        """The single vectors of several streams in one launch on `carrier_sid`; afterwards the
+        members' streamQuery / chi2 / hist read their vector of the carrier."""
+        a = np.ascontiguousarray(args2d, dtype=np.float32)
+        m = np.ascontiguousarray(member_sids, dtype=np.int32)
+        assert a.ndim == 2 and a.shape[1] == n * n + n and m.shape[0] == a.shape[0]
+        self._ck(self.lib.gsm_run_coalesced(self._h, N, carrier_sid, n, a.shape[0], _p(a, _f32p), _p(m, _i32p)))
 
     def run_resident(self, N: int, sid: int):
         self._ck(self.lib.gsm_run_resident(self._h, N, sid))

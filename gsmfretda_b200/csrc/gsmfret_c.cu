@@ -112,6 +112,10 @@ struct Slot {
     long long* d_cnt = nullptr; long long* h_cnt = nullptr;
     int32_t* d_steps = nullptr; int32_t* h_steps = nullptr;
     bool ran = false;
+    // results of this slot live in vector alias_p of slot alias_sid (it was a member of a coalesced
+    // launch, gsm_run_coalesced) until the slot runs by itself again; -1: its own
+    int alias_sid = -1, alias_p = 0;
+    bool per_vector_epochs = false;   // the staged vectors carry their own draw epochs
     uint32_t peer_seq = 0;   // evaluations exchanged on this slot so far
     // reference-draws mode: the per-thread generators of the reference (devQStates / devStates)
     ulonglong2* d_sob_state = nullptr;
@@ -766,6 +770,7 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
         a.peer.timeout_ms = c->peer_timeout_ms;
     }
     a.seed = c->seed; a.epoch0 = s.epoch;
+    a.epoch_per_vector = s.per_vector_epochs ? 1 : 0;
     a.clk_p = c->clk_p; a.bg_ad_rate = c->bg_ad; a.bg_dd_rate = c->bg_dd;
 
     if (c->mode == GSM_MODE_REFERENCE) {
@@ -817,7 +822,9 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
     }
     if (timing) CK(cudaEventRecord(s.ev1, s.stream));
     s.res_P = s.P; s.res_nbp = nbp;
-    s.epoch += (uint32_t)s.P;
+    if (!s.per_vector_epochs) s.epoch += (uint32_t)s.P;   // a coalesced launch advanced its members' epochs instead
+    s.per_vector_epochs = false;
+    s.alias_sid = -1;
     s.ran = true;
     return GSM_OK;
 }
@@ -848,6 +855,51 @@ int gsm_run_batch(gsm_ctx* c, int N, int sid, int n, int P, const float* args)
     return run_common(c, N, sid, true);
 }
 
+// Several stream slots' single vectors in ONE launch on a carrier slot.  Vector p is evaluated
+// with member p's own draw epoch (so the results are the bits the member's own launch would have
+// produced), the member's epoch advances by one as if it had run, and until the member runs by
+// itself again its result accessors (gsm_query, gsm_sync, gsm_result_chi2/hist/flags) read
+// vector p of the carrier.  The carrier must not be a member, and must not be launched again
+// before the members' results have been read.
+int gsm_run_coalesced(gsm_ctx* c, int N, int carrier_sid, int n, int P, const float* args, const int* member_sids)
+{
+    int r = check_sid(c, carrier_sid);
+    if (r) return r;
+    if (P < 1 || !args || !member_sids) return fail(GSM_EINVAL, "coalesced launch of %d vectors", P);
+    if (c->flags & (GSM_KEEP_MCE | GSM_KEEP_COUNTS)) return fail(GSM_ESTATE, "per-sample outputs are kept per stream: no coalesced launches");
+    if (c->mode == GSM_MODE_REFERENCE) return fail(GSM_ESTATE, "reference-draws mode evaluates one vector per launch");
+    for (int p = 0; p < P; ++p) {
+        const int m = member_sids[p];
+        if (m < 0 || m >= (int)c->slots.size() || m == carrier_sid) return fail(GSM_EINVAL, "member %d: stream %d (carrier %d)", p, m, carrier_sid);
+        for (int k = 0; k < p; ++k)
+            if (member_sids[k] == m) return fail(GSM_EINVAL, "stream %d is a member twice", m);
+    }
+    CK(cudaSetDevice(c->devid));
+    Slot& s = c->slots[carrier_sid];
+    r = ensure_params_cap(c, s, P);
+    if (r) return r;
+    CK(cudaStreamSynchronize(s.stream));
+    const int na = n * n + n;
+    for (int p = 0; p < P; ++p) {
+        if (!expand_params(n, args + (size_t)p * na, na, &s.h_params[p]))
+            return fail(GSM_EINVAL, "vector %d: bad parameter vector for %d states", p, n);
+        s.h_params[p].epoch = c->slots[member_sids[p]].epoch;
+    }
+    s.n = n;
+    s.P = P;
+    s.per_vector_epochs = true;
+    r = run_common(c, N, carrier_sid, true);
+    if (r) { s.per_vector_epochs = false; return r; }
+    for (int p = 0; p < P; ++p) {
+        Slot& m = c->slots[member_sids[p]];
+        m.epoch += 1u;
+        m.alias_sid = carrier_sid;
+        m.alias_p = p;
+        m.n = n;
+    }
+    return GSM_OK;
+}
+
 int gsm_run_resident(gsm_ctx* c, int N, int sid)
 {
     int r = check_sid(c, sid);
@@ -856,10 +908,20 @@ int gsm_run_resident(gsm_ctx* c, int N, int sid)
     return run_common(c, N, sid, false);
 }
 
+// where the results of stream sid live: itself, or the carrier of the coalesced launch it was part of
+static inline const Slot& result_slot(const gsm_ctx* c, int sid, int* p_base)
+{
+    const Slot& s = c->slots[sid];
+    if (s.alias_sid >= 0) { *p_base = s.alias_p; return c->slots[s.alias_sid]; }
+    *p_base = 0;
+    return s;
+}
+
 int gsm_query(gsm_ctx* c, int sid)
 {
     if (!c || sid < 0 || sid >= (int)c->slots.size()) return 0;  // mc::streamQuery returns false
-    cudaError_t e = cudaStreamQuery(c->slots[sid].stream);
+    int pb;
+    cudaError_t e = cudaStreamQuery(result_slot(c, sid, &pb).stream);
     if (e == cudaSuccess) return 1;
     if (e == cudaErrorNotReady) { cudaGetLastError(); return 0; }
     return fail(GSM_ECUDA, "cudaStreamQuery returned %s(%d)", cudaGetErrorString(e), (int)e);
@@ -869,27 +931,36 @@ int gsm_sync(gsm_ctx* c, int sid)
 {
     int r = check_sid(c, sid);
     if (r) return r;
-    CK(cudaStreamSynchronize(c->slots[sid].stream));
+    int pb;
+    CK(cudaStreamSynchronize(result_slot(c, sid, &pb).stream));
     return GSM_OK;
 }
 
 float gsm_result_chi2(const gsm_ctx* c, int sid)
 {
-    if (!c || sid < 0 || sid >= (int)c->slots.size() || !c->slots[sid].ran) return NAN;
-    const Slot& s = c->slots[sid];
-    return res_chi2(s.h_res, s.res_P, s.res_nbp)[0];
+    if (!c || sid < 0 || sid >= (int)c->slots.size()) return NAN;
+    int pb;
+    const Slot& s = result_slot(c, sid, &pb);
+    if (!s.ran || pb >= s.res_P) return NAN;
+    return res_chi2(s.h_res, s.res_P, s.res_nbp)[pb];
 }
 const float* gsm_result_chi2v(const gsm_ctx* c, int sid, int* P)
 {
-    if (!c || sid < 0 || sid >= (int)c->slots.size() || !c->slots[sid].ran) return nullptr;
-    const Slot& s = c->slots[sid];
-    if (P) *P = s.res_P;
-    return res_chi2(s.h_res, s.res_P, s.res_nbp);
+    if (!c || sid < 0 || sid >= (int)c->slots.size()) return nullptr;
+    int pb;
+    const Slot& s = result_slot(c, sid, &pb);
+    if (!s.ran || pb >= s.res_P) return nullptr;
+    if (P) *P = c->slots[sid].alias_sid >= 0 ? 1 : s.res_P;
+    return res_chi2(s.h_res, s.res_P, s.res_nbp) + pb;
 }
 const uint64_t* gsm_result_hist(const gsm_ctx* c, int sid, int p)
 {
-    if (!c || sid < 0 || sid >= (int)c->slots.size() || !c->slots[sid].ran) return nullptr;
-    const Slot& s = c->slots[sid];
+    if (!c || sid < 0 || sid >= (int)c->slots.size()) return nullptr;
+    int pb;
+    const Slot& s = result_slot(c, sid, &pb);
+    if (!s.ran) return nullptr;
+    if (c->slots[sid].alias_sid >= 0 && p != 0) return nullptr;   // a member owns one vector of the carrier
+    p += pb;
     if (p < 0 || p >= s.res_P) return nullptr;
     return (const uint64_t*)(res_hist(s.h_res) + (size_t)p * s.res_nbp);
 }
@@ -919,8 +990,10 @@ int gsm_result_timing(const gsm_ctx* c, int sid, uint64_t out_ns[4])
 
 uint64_t gsm_result_flags(const gsm_ctx* c, int sid)
 {
-    if (!c || sid < 0 || sid >= (int)c->slots.size() || !c->slots[sid].ran) return 0;
-    return ((const ResultHeader*)c->slots[sid].h_res)->flags;
+    if (!c || sid < 0 || sid >= (int)c->slots.size()) return 0;
+    int pb;
+    const Slot& s = result_slot(c, sid, &pb);
+    return s.ran ? ((const ResultHeader*)s.h_res)->flags : 0;
 }
 float gsm_last_elapsed_ms(gsm_ctx* c, int sid)
 {

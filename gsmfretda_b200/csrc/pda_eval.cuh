@@ -42,7 +42,13 @@ constexpr uint32_t kStepCap = 1u << 20; // guards the GPU against rates <= 0 (a 
 constexpr int kFifoD = PDA_FIFO_D;       // entries per lane (a trip adds at most 3: start, draw, end)
 constexpr int kFetchTh = PDA_FETCH_TH;   // lanes that must be waiting before the merged loop stops to fetch
 constexpr uint32_t kEntDraw = 0u, kEntStart = 1u, kEntEnd = 2u;
-static_assert(kFifoD >= 4 && kFifoD <= 16, "two kind bits per entry live in one 32-bit register");
+#ifdef PDA_NO_DEFER
+constexpr bool kDeferDraws = false;      // A/B builds: every draw taken where it arises, as before
+#else
+constexpr bool kDeferDraws = true;
+#endif
+template <int kMode> struct Defers { static constexpr bool value = kDeferDraws && kMode == kModeReplay; };
+static_assert(kFifoD >= 5 && kFifoD <= 17, "two kind bits per entry live in one 32-bit register");
 
 // parameter vector staged in shared memory, with the per-state terms hoisted
 struct SmemParams {
@@ -261,7 +267,7 @@ __device__ __forceinline__ void lane_begin(Lane& L, const SmemParams& sp, const 
     }
     // replay mode: the xor128 stream of the sample is seeded from its step-0 block (lane_step)
     L.F = 0.0f; L.spent = 0.0f;
-    if (kMode != kModeReplay) L.acc = 0.0f;   // replay: the queue's start entry resets it (the consumer owns acc and xs)
+    if (!Defers<kMode>::value) L.acc = 0.0f;   // deferred draws: the queue's start entry resets it (the consumer owns acc and xs)
     L.fb = (float)L.start;
     L.first = 0;
     L.step = 0;
@@ -308,7 +314,8 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
         if (kFast) iw = (w.x & 0xffu) | ((w.y & 0xffu) << 8) | ((w.z & 0xffu) << 16) | (w.w << 24);
         else if (!kSobol) {
             iw = ((w.x & 0xffu) << 24) | ((w.y & 0xffu) << 16) | ((w.z & 0xffu) << 8) | 0x80u;
-            seed_out = w.w;
+            if (Defers<kMode>::value) seed_out = w.w;
+            else L.xs.seed((uint64_t)w.w);
         }
         L.si = pick(sp.cumP, n, u01(iw));
     }
@@ -403,7 +410,7 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
             if (kSobol) w.z = (uint32_t)(sobol_next(L) >> 32);
             const float rd = det_norm_icdf(w.z) * sp.v[si] + sp.rootE[si];
             const float de = 1.0f / (1.0f + det_pow6f(rd / kR0));
-            if (kMode == kModeReplay) {
+            if (Defers<kMode>::value) {
                 has_draw = true;
                 draw_n = (int)f_i;
                 draw_p = de;
@@ -412,7 +419,7 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
             }
         }
     }
-    if (kMode != kModeReplay) L.acc += (float)ai;
+    if (!Defers<kMode>::value) L.acc += (float)ai;
     L.si = sj;
     L.step++;
 }
@@ -578,6 +585,179 @@ __device__ __forceinline__ void peer_exchange_block(const EvalArgs& a, unsigned 
     __syncthreads();
 }
 
+// Dynamic shared memory of the evaluation kernel: per-warp histograms, then (deferred draws) per warp
+// kFifoD rows of 32 16-byte queue entries — row 0 holds the lanes' xor128 streams, rows 1.. the
+// entries, entry e of lane l at [(1 + e) * 32 + l] (conflict-free) — the list of the entries that are
+// draws (2 B each, filled in arrival order, read 32 at a time), and the lanes' acceptor sums.
+struct QueueView {
+    unsigned int* hist;        // this warp's histogram
+    uint4* state;              // [32] xor128 stream of each lane's consumer
+    uint4* fifo;               // [(kFifoD - 1) * 32]
+    unsigned short* drawref;   // [(kFifoD - 1) * 32]
+    float* acc;                // [32]
+};
+constexpr int kFifoCap = kFifoD - 1;   // entries a lane can hold
+__device__ __forceinline__ QueueView queue_view(int nb)
+{
+    extern __shared__ __align__(16) unsigned int s_dyn[];
+    constexpr int kWarps = kBlock / 32;
+    const int wid = threadIdx.x >> 5;
+    const int nbp = nb + 2;
+    uint4* q0 = reinterpret_cast<uint4*>(s_dyn + ((kWarps * nbp + 3) & ~3));
+    unsigned short* d0 = reinterpret_cast<unsigned short*>(q0 + kWarps * (kFifoD * 32));
+    float* a0 = reinterpret_cast<float*>(d0 + kWarps * (kFifoD * 32));
+    QueueView v;
+    v.hist = s_dyn + wid * nbp;
+    v.state = q0 + wid * (kFifoD * 32);
+    v.fifo = v.state + 32;
+    v.drawref = d0 + wid * (kFifoD * 32);
+    v.acc = a0 + wid * 32;
+    return v;
+}
+
+// Deferred draws: work the draw queues of one warp off (called by all 32 lanes).  A call, not
+// inlined: the merged loop below needs most of the register file, and this way the walk state of
+// the lanes is parked once per call instead of the loop's variables being spilled on every trip;
+// for the same reason the consumer state of a lane (the xor128 stream and the acceptor sum of the
+// sample its queue is in the middle of) lives in shared memory, not in registers of the walk.
+static __device__ __noinline__ void drain_draw_queues(const EvalArgs& a, const double2* __restrict__ ltab, int q_cnt,
+                                                      uint32_t q_kinds, int w_draws)
+{
+    const int lane = threadIdx.x & 31;
+    const QueueView v = queue_view(a.nb);
+    // pass 1: q^n = exp(n log(1 - p)) of every recorded draw that the inversion will take,
+    // the draws of all lanes dealt 32 at a time (no order among them: nothing is drawn yet)
+    for (int k = lane; k < w_draws; k += 32) {
+        uint4* ent = v.fifo + v.drawref[k];
+        const int n = (int)ent->x;
+        const double p = (double)__uint_as_float(ent->y);
+        const bool no_trials = n <= 0 && n >= -64 && p > 0.0 && p < 1.0;
+        const double pp = !(p <= 0.5) ? 1.0 - p : p;
+        if (!no_trials && pp * (double)n <= 30.0) {
+            const double qn = det_exp((double)n * det_log(1.0 - pp, ltab));
+            ent->z = (uint32_t)__double2loint(qn);
+            ent->w = (uint32_t)__double2hiint(qn);
+        }
+    }
+    __syncwarp();
+    // pass 2: every lane walks its own queue in order on the sample's xor128 stream; the
+    // inversion loops (role of rk_binomial_inversion, binom.cuh:135-169) of the lanes are ONE
+    // loop, a lane that finishes a draw waits until enough others have to fetch the next
+    const bool keep_samples = a.mcE || a.sum_ai || a.n_steps;
+    int rd = 0;
+    bool have = false, mir = false, cold = false;
+    int n = 0, X = 0, bound = 0;
+    double pp = 0.0, px = 1.0, U = 0.0, dX = 0.0, dn1 = 1.0;
+    for (;;) {
+        for (;;) {
+            const unsigned idle = __ballot_sync(0xffffffffu, !have && !cold && rd < q_cnt);
+            const unsigned busy = __ballot_sync(0xffffffffu, have);
+            if ((idle | busy) == 0u) break;
+            if (idle != 0u && (busy == 0u || __popc(idle) >= kFetchTh)) {
+                if (!have && !cold) {
+                    while (rd < q_cnt) {
+                        const uint4 ent = v.fifo[rd * 32 + lane];
+                        const uint32_t kind = (q_kinds >> (2 * rd)) & 3u;
+                        ++rd;
+                        if (kind == kEntStart) {
+                            Xor128 xs;
+                            xs.seed((uint64_t)ent.y);   // role of setup_kernel's rk_seed, gen_rand.cuh:19-21
+                            v.state[lane] = make_uint4(xs.s0, xs.s1, xs.s2, xs.s3);
+                            v.acc[lane] = 0.0f;
+                        } else if (kind == kEntEnd) {
+                            // IEEE division in both modes: E takes few distinct values (small integer
+                            // counts), so a 1-ulp difference would move whole atoms of the distribution.
+                            // 0 / F = +0 is spelled out: a zero numerator sends the division through its slow path.
+                            const float F = __uint_as_float(ent.y);
+                            const float acc = v.acc[lane];
+                            const float e = (F > 0.0f && acc != 0.0f) ? __fdiv_rn(acc, F) : 0.0f;
+                            if (keep_samples) {
+                                const size_t oi = ((size_t)ent.w << 32) | (size_t)ent.z;
+                                if (a.mcE) a.mcE[oi] = e;
+                                if (a.sum_ai) a.sum_ai[oi] = (long long)acc;   // integer-valued, exact below 2^24
+                                if (a.n_steps) a.n_steps[oi] = (int32_t)ent.x;
+                            }
+                            const int bin = hist_index(e, a.nb);
+                            const unsigned fm = __activemask();
+                            const unsigned peers = __match_any_sync(fm, bin);
+                            if (lane == __ffs(peers) - 1) atomicAdd(&v.hist[bin], (unsigned)__popc(peers));
+                        } else {
+                            // the cases of binomial() (pda_device.cuh), in its order
+                            n = (int)ent.x;
+                            const double p = (double)__uint_as_float(ent.y);
+                            if (n <= 0 && n >= -64 && p > 0.0 && p < 1.0) {
+                                const uint4 st = v.state[lane];
+                                Xor128 xs{st.x, st.y, st.z, st.w};
+                                xs.next();
+                                xs.next();
+                                v.state[lane] = make_uint4(xs.s0, xs.s1, xs.s2, xs.s3);
+                                if (!(p <= 0.5)) v.acc[lane] += (float)n;
+                                continue;
+                            }
+                            mir = !(p <= 0.5);
+                            pp = mir ? 1.0 - p : p;
+                            if (pp * (double)n <= 30.0) {
+                                bound = n;
+                                if (n < 1 || n > 10) {
+                                    const double np = (double)n * pp;
+                                    double bd = np + 10.0 * __dsqrt_rn(np * (1.0 - pp) + 1.0);
+                                    if (!(bd <= (double)n)) bd = (double)n;
+                                    bound = (int)bd;
+                                }
+                                X = 0;
+                                dX = 0.0;
+                                dn1 = (double)n + 1.0;
+                                px = __hiloint2double((int)ent.w, (int)ent.z);   // q^n from pass 1
+                                const uint4 st = v.state[lane];
+                                Xor128 xs{st.x, st.y, st.z, st.w};
+                                U = xs.next_double();
+                                v.state[lane] = make_uint4(xs.s0, xs.s1, xs.s2, xs.s3);
+                                have = true;
+                            } else {
+                                cold = true;   // BTPE: taken below, outside the merged loop
+                            }
+                            break;
+                        }
+                    }
+                }
+            }
+            if (have) {
+                if (U > px) {
+                    X++;
+                    dX += 1.0;
+                    if (X > bound) {   // start over with a fresh uniform (binom.cuh:157-161); q^n is still in the entry
+                        const uint4 ent = v.fifo[(rd - 1) * 32 + lane];
+                        X = 0;
+                        dX = 0.0;
+                        px = __hiloint2double((int)ent.w, (int)ent.z);
+                        const uint4 st = v.state[lane];
+                        Xor128 xs{st.x, st.y, st.z, st.w};
+                        U = xs.next_double();
+                        v.state[lane] = make_uint4(xs.s0, xs.s1, xs.s2, xs.s3);
+                    } else {
+                        U -= px;
+                        px = ((dn1 - dX) * pp * px) / (dX * (1.0 - pp));
+                    }
+                } else {
+                    v.acc[lane] += (float)(mir ? n - X : X);
+                    have = false;
+                }
+            }
+        }
+        have = false;   // (it is: no lane was busy) — nothing of the inversion lives across the call below
+        if (!__any_sync(0xffffffffu, cold)) break;
+        if (cold) {
+            const uint4 st = v.state[lane];
+            Xor128 t{st.x, st.y, st.z, st.w};
+            const long long Xb = binomial_btpe(t, n, pp);
+            v.state[lane] = make_uint4(t.s0, t.s1, t.s2, t.s3);
+            v.acc[lane] += (float)(int)(mir ? (long long)n - Xb : Xb);
+            cold = false;
+        }
+    }
+    __syncwarp();
+}
+
 // Persistent, warp-autonomous evaluation kernel.
 //   kLayout 0: raw int64 burst_ad/burst_dd (fallback), 1: packed words scanned photon by
 //   photon, 2: packed words + running-max / next-photon index (O(log ph) windows).
@@ -613,13 +793,8 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
     const int nbp = a.nb + 2;
     SmemParams& sp = s_params[wid];
     unsigned int* hist = s_hist_all + wid * nbp;
-    // replay mode: the warp's draw queues, entry e of lane l at [e * 32 + l] (conflict-free), and
-    // the list of the entries that are draws (filled in arrival order, read 32 at a time)
-    constexpr bool kDefer = kMode == kModeReplay;
-    uint4* fifo = reinterpret_cast<uint4*>(s_hist_all + ((kWarps * nbp + 3) & ~3)) + wid * (kFifoD * 32);
-    unsigned short* drawref = reinterpret_cast<unsigned short*>(
-                                  reinterpret_cast<uint4*>(s_hist_all + ((kWarps * nbp + 3) & ~3)) + kWarps * (kFifoD * 32)) +
-                              wid * (kFifoD * 32);
+    constexpr bool kDefer = Defers<kMode>::value;
+    const QueueView qv = queue_view(a.nb);   // pointers are only used in deferred mode
 
     const int64_t per_p = a.N * (int64_t)a.R;  // samples per parameter vector
     const unsigned long long chunks_per_p = (unsigned long long)((per_p + a.chunk - 1) >> a.chunk_log2);
@@ -697,7 +872,10 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
                     }
                     __syncwarp();
                     stage_params(sp, a.use_inl ? &a.inl : a.params + p, lane);
-                    if (lane == 0) { wc.cur_p = p; wc.epoch = a.epoch0 + (uint32_t)p; }
+                    if (lane == 0) {
+                        wc.cur_p = p;
+                        wc.epoch = a.epoch_per_vector ? (a.use_inl ? a.inl.epoch : a.params[p].epoch) : a.epoch0 + (uint32_t)p;
+                    }
                     __syncwarp();
                 }
                 const unsigned long long c = item - (unsigned long long)p * chunks_per_p;
@@ -754,116 +932,12 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
         // ---- replay mode: work the draw queues off -----------------------------------------
         // when a queue could overflow in the coming trip, before the histogram changes hands, and
         // when the warp has nothing else left
-        if (kDefer && (drain || none_active || __any_sync(0xffffffffu, q_cnt > kFifoD - 3)) &&
+        if (kDefer && (drain || none_active || __any_sync(0xffffffffu, q_cnt > kFifoCap - 3)) &&
             __any_sync(0xffffffffu, q_cnt > 0)) {
-            // pass 1: q^n = exp(n log(1 - p)) of every recorded draw that the inversion will take,
-            // the draws of all lanes dealt 32 at a time (no order among them: nothing is drawn yet)
-            for (int k = lane; k < w_draws; k += 32) {
-                uint4* ent = fifo + drawref[k];
-                const int n = (int)ent->x;
-                const double p = (double)__uint_as_float(ent->y);
-                const bool no_trials = n <= 0 && n >= -64 && p > 0.0 && p < 1.0;
-                const double pp = !(p <= 0.5) ? 1.0 - p : p;
-                if (!no_trials && pp * (double)n <= 30.0) {
-                    const double qn = det_exp((double)n * det_log(1.0 - pp, s_logtab));
-                    ent->z = (uint32_t)__double2loint(qn);
-                    ent->w = (uint32_t)__double2hiint(qn);
-                }
-            }
-            __syncwarp();
-            // pass 2: every lane walks its own queue in order on the sample's xor128 stream; the
-            // inversion loops (role of rk_binomial_inversion, binom.cuh:135-169) of the lanes are ONE
-            // loop, a lane that finishes a draw waits until enough others have to fetch the next
-            int rd = 0;
-            bool have = false, mir = false;
-            int n = 0, X = 0, bound = 0;
-            double pp = 0.0, q = 1.0, qn = 1.0, px = 1.0, U = 0.0, dX = 0.0, dn1 = 1.0;
-            for (;;) {
-                const unsigned idle = __ballot_sync(0xffffffffu, !have && rd < q_cnt);
-                const unsigned busy = __ballot_sync(0xffffffffu, have);
-                if ((idle | busy) == 0u) break;
-                if (idle != 0u && (busy == 0u || __popc(idle) >= kFetchTh)) {
-                    if (!have) {
-                        while (rd < q_cnt) {
-                            const uint4 ent = fifo[rd * 32 + lane];
-                            const uint32_t kind = (q_kinds >> (2 * rd)) & 3u;
-                            ++rd;
-                            if (kind == kEntStart) {
-                                L.xs.seed((uint64_t)ent.y);   // role of setup_kernel's rk_seed, gen_rand.cuh:19-21
-                                L.acc = 0.0f;
-                            } else if (kind == kEntEnd) {
-                                // IEEE division in both modes: E takes few distinct values (small integer
-                                // counts), so a 1-ulp difference would move whole atoms of the distribution.
-                                // 0 / F = +0 is spelled out: a zero numerator sends the division through its slow path.
-                                const float F = __uint_as_float(ent.y);
-                                const float e = (F > 0.0f && L.acc != 0.0f) ? __fdiv_rn(L.acc, F) : 0.0f;
-                                if (keep_samples) {
-                                    const size_t oi = ((size_t)ent.w << 32) | (size_t)ent.z;
-                                    if (a.mcE) a.mcE[oi] = e;
-                                    if (a.sum_ai) a.sum_ai[oi] = (long long)L.acc;   // integer-valued, exact below 2^24
-                                    if (a.n_steps) a.n_steps[oi] = (int32_t)ent.x;
-                                }
-                                const int bin = hist_index(e, a.nb);
-                                const unsigned fm = __activemask();
-                                const unsigned peers = __match_any_sync(fm, bin);
-                                if (lane == __ffs(peers) - 1) atomicAdd(&hist[bin], (unsigned)__popc(peers));
-                            } else {
-                                // the cases of binomial() (pda_device.cuh), in its order
-                                n = (int)ent.x;
-                                const double p = (double)__uint_as_float(ent.y);
-                                if (n <= 0 && n >= -64 && p > 0.0 && p < 1.0) {
-                                    L.xs.next();
-                                    L.xs.next();
-                                    L.acc += (float)(p <= 0.5 ? 0 : n);
-                                    continue;
-                                }
-                                mir = !(p <= 0.5);
-                                pp = mir ? 1.0 - p : p;
-                                if (pp * (double)n <= 30.0) {
-                                    q = 1.0 - pp;
-                                    qn = __hiloint2double((int)ent.w, (int)ent.z);
-                                    bound = n;
-                                    if (n < 1 || n > 10) {
-                                        const double np = (double)n * pp;
-                                        double bd = np + 10.0 * __dsqrt_rn(np * q + 1.0);
-                                        if (!(bd <= (double)n)) bd = (double)n;
-                                        bound = (int)bd;
-                                    }
-                                    X = 0;
-                                    dX = 0.0;
-                                    dn1 = (double)n + 1.0;
-                                    px = qn;
-                                    U = L.xs.next_double();
-                                    have = true;
-                                    break;
-                                }
-                                Xor128 t = L.xs;
-                                const long long Xb = binomial_btpe(t, n, pp);
-                                L.xs = t;
-                                L.acc += (float)(int)(mir ? (long long)n - Xb : Xb);
-                            }
-                        }
-                    }
-                }
-                if (have) {
-                    if (U > px) {
-                        X++;
-                        dX += 1.0;
-                        if (X > bound) {
-                            X = 0;
-                            dX = 0.0;
-                            px = qn;
-                            U = L.xs.next_double();
-                        } else {
-                            U -= px;
-                            px = ((dn1 - dX) * pp * px) / (dX * q);
-                        }
-                    } else {
-                        L.acc += (float)(mir ? n - X : X);
-                        have = false;
-                    }
-                }
-            }
+            // (a call, not inlined: the callee gets the whole register file for the merged loop, the
+            // walk state of the lanes is parked in local memory once per call instead of the loop's
+            // variables being spilled on every trip)
+            drain_draw_queues(a, s_logtab, q_cnt, q_kinds, w_draws);
             q_cnt = 0;
             q_kinds = 0u;
             w_draws = 0;
@@ -913,22 +987,22 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
         if (kDefer) {
             // record what the window left to do, in the order the sample needs it
             if (first_step) {
-                fifo[q_cnt * 32 + lane].y = seed;
+                qv.fifo[q_cnt * 32 + lane].y = seed;
                 q_kinds |= kEntStart << (2 * q_cnt);
                 ++q_cnt;
             }
             const unsigned dm = __ballot_sync(0xffffffffu, has_draw);
             if (has_draw) {
                 const int at = q_cnt * 32 + lane;
-                fifo[at].x = (uint32_t)draw_n;
-                fifo[at].y = __float_as_uint(draw_p);
-                drawref[w_draws + __popc(dm & lt_mask)] = (unsigned short)at;
+                qv.fifo[at].x = (uint32_t)draw_n;
+                qv.fifo[at].y = __float_as_uint(draw_p);
+                qv.drawref[w_draws + __popc(dm & lt_mask)] = (unsigned short)at;
                 ++q_cnt;                         // kEntDraw = 0: no kind bits to set
             }
             w_draws += __popc(dm);
             if (fin) {
                 const size_t oi = (size_t)wc.cur_p * (size_t)per_p + (size_t)L.bl * (size_t)a.R + L.rep;
-                fifo[q_cnt * 32 + lane] = make_uint4(L.step, __float_as_uint(L.F), (uint32_t)oi, (uint32_t)((unsigned long long)oi >> 32));
+                qv.fifo[q_cnt * 32 + lane] = make_uint4(L.step, __float_as_uint(L.F), (uint32_t)oi, (uint32_t)((unsigned long long)oi >> 32));
                 q_kinds |= kEntEnd << (2 * q_cnt);
                 ++q_cnt;
             }
@@ -979,8 +1053,12 @@ template <int kLayout, bool kBg, int kMode>
 static int resident_blocks(size_t dyn)
 {
     int nb = 0;
-    if (dyn > 48 * 1024)
-        cudaFuncSetAttribute(pda_eval_kernel<kLayout, kBg, kMode>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+    // static + dynamic shared memory beyond 48 KB per block needs the opt-in; the value is a cap
+    cudaFuncAttributes fa{};
+    cudaFuncGetAttributes(&fa, pda_eval_kernel<kLayout, kBg, kMode>);
+    if (dyn + fa.sharedSizeBytes > 48 * 1024)
+        cudaFuncSetAttribute(pda_eval_kernel<kLayout, kBg, kMode>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)(dyn > 64 * 1024 ? dyn : 64 * 1024));
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, pda_eval_kernel<kLayout, kBg, kMode>, kBlock, dyn);
     return nb < 1 ? 1 : nb;
 }
@@ -990,7 +1068,7 @@ template <int kMode>
 static inline size_t eval_dyn_smem(int nb)
 {
     const size_t hist_words = ((size_t)(kBlock / 32) * (size_t)(nb + 2) + 3) & ~(size_t)3;
-    const size_t queues = kMode == kModeReplay ? (size_t)(kBlock / 32) * kFifoD * 32 * (16 + 2) : 0;
+    const size_t queues = Defers<kMode>::value ? (size_t)(kBlock / 32) * kFifoD * 32 * (16 + 2) + kBlock * sizeof(float) : 0;
     return hist_words * sizeof(unsigned int) + queues;
 }
 

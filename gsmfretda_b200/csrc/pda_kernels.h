@@ -36,6 +36,7 @@ struct ParamRaw {
     float K[64];      // column-major n x n, K(i,j) = rate j -> i
     float P_i2j[64];  // column-major n x n
     float p[8];       // unnormalised inflow rates
+    uint32_t epoch;   // draw epoch of this vector when EvalArgs::epoch_per_vector (coalesced launches)
 };
 
 // Cross-GPU histogram exchange fused into the evaluation kernel (burst-split sharding,
@@ -84,7 +85,8 @@ struct EvalArgs {
     int32_t finalize;          // 1: the last block reduces chi2 and resets the working set
                                // 2: the same after the peer exchange (PeerArgs); 0: leave whist for a library all-reduce
     uint32_t seed;
-    uint32_t epoch0;           // parameter vector p draws with epoch0 + p
+    uint32_t epoch0;           // parameter vector p draws with epoch0 + p ...
+    int32_t epoch_per_vector;  // ... or, when set, with its own ParamRaw::epoch
     float clk_p, bg_ad_rate, bg_dd_rate;
     PeerArgs peer;
     // reference-draws mode (GSM_MODE_REFERENCE): the reference's per-thread generators

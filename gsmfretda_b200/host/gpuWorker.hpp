@@ -20,8 +20,15 @@ class gpuWorker {
           dataready(_dataready), s_n(_sn), params(_params), N(_N), ga_start(_ga_start),
           ga_stop(_ga_stop), debug(debugbool) {}
 
-    void run(int /*sz_burst*/)
+    // Coalescing (not in the reference): when at least `min_group` streams hold a single vector of
+    // the same model over the same burst range at the same moment, they are evaluated by ONE launch
+    // on a carrier slot of the `mc` (mc::run_coalesced; every vector keeps its own stream's draw
+    // epoch, so the results are the bits of the per-stream launches).  0 switches it off.
+    void set_coalesce(int min_group) { coalesce_min = (pdamc->carriers() > 0) ? min_group : 0; }
+
+    void run(int sz_burst)
     {
+        if (coalesce_min > 0) { run_coalescing(sz_burst); return; }
         pdamc->set_gpuid();
         do {
             for (int sid = 0; sid < streamNum; ++sid) {
@@ -45,6 +52,83 @@ class gpuWorker {
     }
 
   private:
+    // One pass over the streams keeps the locks of those with a vector ready, groups them by
+    // (states, bursts), launches each group of min_group or more on a free carrier and the rest one
+    // by one, and only then lets the streams go.  A carrier is free again when its launch has
+    // finished and every member has been seen past "results ready" (its results are read).
+    void run_coalescing(int /*sz_burst*/)
+    {
+        pdamc->set_gpuid();
+        const int C = pdamc->carriers();
+        std::vector<std::vector<int>> riding((size_t)C);
+        std::vector<int> seen((size_t)streamNum, -1), ready, group;
+        std::vector<std::unique_lock<std::mutex>> held;
+        std::vector<float> args;
+        do {
+            ready.clear();
+            held.clear();
+            for (int sid = 0; sid < streamNum; ++sid) {
+                std::unique_lock<std::mutex> lck(_m[sid], std::defer_lock);
+                seen[(size_t)sid] = -1;
+                if (!lck.try_lock()) continue;
+                const int st = dataready[sid];
+                seen[(size_t)sid] = st;
+                if (st == 3) {
+                    const bool done = pdamc->streamQuery(sid);
+                    if (done) dataready[sid] = 4;
+                    lck.unlock();
+                    if (done) _cv[sid].notify_one();
+                } else if (st == 2) {
+                    ready.push_back(sid);
+                    held.push_back(std::move(lck));
+                }
+            }
+            for (int c = 0; c < C; ++c) {
+                if (riding[(size_t)c].empty() || !pdamc->carrierQuery(c)) continue;
+                bool read = true;
+                for (int sid : riding[(size_t)c]) read = read && seen[(size_t)sid] >= 0 && seen[(size_t)sid] != 3 && seen[(size_t)sid] != 4;
+                if (read) riding[(size_t)c].clear();
+            }
+            std::vector<char> taken(ready.size(), 0);
+            for (size_t i = 0; i < ready.size(); ++i) {
+                if (taken[i]) continue;
+                const int sid = ready[i], n = s_n[sid];
+                const size_t per_vector = (size_t)n * (size_t)(n + 1);
+                int carrier = -1;
+                for (int c = 0; c < C && carrier < 0; ++c)
+                    if (riding[(size_t)c].empty()) carrier = c;
+                group.clear();
+                if (carrier >= 0 && n >= 2 && params[sid].size() == per_vector) {
+                    for (size_t k = i; k < ready.size(); ++k) {
+                        const int o = ready[k];
+                        if (!taken[k] && s_n[o] == n && params[o].size() == per_vector && ga_start[o] == ga_start[sid] &&
+                            ga_stop[o] == ga_stop[sid])
+                            group.push_back(o);
+                    }
+                }
+                if ((int)group.size() >= coalesce_min) {
+                    args.clear();
+                    for (int o : group) args.insert(args.end(), params[o].begin(), params[o].end());
+                    const int Ng = pdamc->setBurstBd(ga_start[sid], ga_stop[sid], sid);
+                    if (pdamc->run_coalesced(carrier, n, Ng, group, args)) {
+                        for (int o : group) {
+                            N[o] = Ng;
+                            dataready[o] = 3;
+                            for (size_t k = i; k < ready.size(); ++k)
+                                if (ready[k] == o) taken[k] = 1;
+                        }
+                        riding[(size_t)carrier] = group;
+                        continue;
+                    }
+                }
+                launch(sid);
+                dataready[sid] = 3;
+                taken[i] = 1;
+            }
+            held.clear();   // unlocks
+        } while (pdamc->workerNum.load() > 0);
+    }
+
     // the six calls of gpuWorker.cpp:71-80, in the reference's order.  params[sid] holding a
     // whole number P > 1 of vectors is a batch (streamWorker::fetch): staged with
     // set_params_batch and evaluated by the same run_kernel in one launch.  A vector the library
@@ -82,4 +166,5 @@ class gpuWorker {
     int* ga_start;
     int* ga_stop;
     unsigned char debug;
+    int coalesce_min = 0;
 };

@@ -4,7 +4,10 @@
 // reference-shaped host API end to end — share_var_init's arrays, the dataready state machine,
 // the six mc calls per evaluation — and reports chi-square per vector from the fused kernel.
 //
-//   local_node <bursts.bin> <params.txt> <out.txt> [streams=4] [reSampleTimes=4] [seed]
+//   local_node <bursts.bin> <params.txt> <out.txt> [streams=4] [reSampleTimes=4] [seed] [coalesce=0]
+//
+// coalesce = K > 0: the gpuWorker thread evaluates K or more vectors that are ready at the same moment
+// with ONE launch (gpuWorker::set_coalesce); the output is the same, bit for bit.
 //
 // bursts.bin (little endian), written by gsmfretda_b200.synth.save_bin:
 //   "GSMB" u32 version=1, i64 B, i64 Nph, f32 clk_p, f32 bg_ad, f32 bg_dd, f32 pad,
@@ -25,6 +28,7 @@
 // unchanged against host/mc.hpp and linked in the place of this node's own gpuWorker
 #ifndef GSM_GPUWORKER_HEADER
 #define GSM_GPUWORKER_HEADER "gpuWorker.hpp"
+#define GSM_NODE_OWN_GPUWORKER 1
 #endif
 #include GSM_GPUWORKER_HEADER
 
@@ -35,10 +39,11 @@ static bool rd(FILE* f, std::vector<T>& v, size_t n) { v.resize(n); return n == 
 
 int main(int argc, char** argv)
 {
-    if (argc < 4) { std::fprintf(stderr, "usage: %s bursts.bin params.txt out.txt [streams] [R] [seed]\n", argv[0]); return 2; }
+    if (argc < 4) { std::fprintf(stderr, "usage: %s bursts.bin params.txt out.txt [streams] [R] [seed] [coalesce]\n", argv[0]); return 2; }
     const int nstreams = argc > 4 ? std::atoi(argv[4]) : 4;
     const int R = argc > 5 ? std::atoi(argv[5]) : 4;
     const uint32_t seed = argc > 6 ? (uint32_t)std::strtoul(argv[6], nullptr, 10) : 1u;
+    const int coalesce = argc > 7 ? std::atoi(argv[7]) : 0;
 
     FILE* f = std::fopen(argv[1], "rb");
     if (!f) { std::perror(argv[1]); return 1; }
@@ -56,6 +61,7 @@ int main(int argc, char** argv)
       while (std::getline(in, line)) { std::istringstream ss(line); Job j; if (!(ss >> j.n)) continue; float x; while (ss >> x) j.args.push_back(x); j.idx = (int)jobs.size(); jobs.push_back(j); } }
 
     mc::Options opt; opt.keep_mce = false; opt.seed = seed;
+    opt.carriers = coalesce > 0 ? 4 : 0;
     mc pdamc(0, nstreams, 0, 0, false, opt);
     int streamNum = 0; pdamc.getStreams(&streamNum);
     pdamc.set_reSampleTimes_exact(R);
@@ -97,6 +103,9 @@ int main(int argc, char** argv)
     std::vector<std::thread> th;
     for (int sid = 0; sid < streamNum; ++sid) th.emplace_back(param_thread, sid);
     gpuWorker gw(&pdamc, streamNum, &sg, opt.fret_hist_num, _m, _cv, dataready, s_n, params, ga_start, ga_stop, N, 0);
+#ifdef GSM_NODE_OWN_GPUWORKER
+    gw.set_coalesce(coalesce);
+#endif
     std::thread tg(&gpuWorker::run, &gw, (int)B);
     for (auto& t : th) t.join();
     tg.join();

@@ -58,6 +58,7 @@ static void usage()
         "      --epoch-from-idx      reproducible draws per parameter index  (default=off)\n"
         "      --host-hist           host histogram and chi-square, as the reference  (default=off)\n"
         "      --max-batch=INT       most vectors per batched p_ga when the node spans GPUs  (default=`64')\n"
+        "      --coalesce=INT        evaluate INT or more vectors that are ready together in one launch, 0 = off  (default=`0')\n"
         "      --oversubscribe       allow a GPU to appear twice in -g (test rigs)  (default=off)\n";
 }
 
@@ -91,7 +92,7 @@ static int show_gpus(int only)   // role of showGPUsInfo (mc.cu:26-59) through t
 int main(int argc, char* argv[])
 {
     std::string url = "tcp://127.0.0.1:7777", input, pidfile, mode = "replay";
-    int gpuid = 0, fretHistNum = 200, streamNum = 0, R = 4, max_batch = 64;
+    int gpuid = 0, fretHistNum = 200, streamNum = 0, R = 4, max_batch = 64, coalesce = 0;
     std::vector<int> gpu_list;   // -g 0,1,2: ONE node over several GPUs (the dataset is split)
     bool gpuid_given = false, gpuinfo = false, profiler = false, epoch_from_idx = false, host_hist = false, oversubscribe = false;
     unsigned char debuglevel = 0;
@@ -107,7 +108,8 @@ int main(int argc, char* argv[])
         {"pid", required_argument, 0, 'I'}, {"resample-times", required_argument, 0, 1000},
         {"mode", required_argument, 0, 1001}, {"seed", required_argument, 0, 1002},
         {"epoch-from-idx", no_argument, 0, 1003}, {"host-hist", no_argument, 0, 1004},
-        {"oversubscribe", no_argument, 0, 1005}, {"max-batch", required_argument, 0, 1006}, {0, 0, 0, 0}};
+        {"oversubscribe", no_argument, 0, 1005}, {"max-batch", required_argument, 0, 1006},
+        {"coalesce", required_argument, 0, 1007}, {0, 0, 0, 0}};
     int c;
     while ((c = getopt_long(argc, argv, "hVu:i:g:f:DCGNKqPs:p:I:", lo, nullptr)) != -1) {
         switch (c) {
@@ -150,6 +152,7 @@ int main(int argc, char* argv[])
                 setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);   // before the first CUDA call
                 break;
             case 1006: max_batch = std::atoi(optarg); break;
+            case 1007: coalesce = std::atoi(optarg); break;
             default: return EXIT_FAILURE;
         }
     }
@@ -195,6 +198,7 @@ int main(int argc, char* argv[])
     opt.left_pad = 2;                  // main.cpp:155
     opt.peer_shared_device = oversubscribe;
     opt.max_batch = max_batch;         // most vectors one batched p_ga may carry when the node spans GPUs
+    opt.carriers = coalesce > 0 ? 4 : 0;   // slots for launches that evaluate several streams' vectors at once
     if (gpu_list.empty()) gpu_list.push_back(gpuid);
     if (gpu_list.size() > 1 && host_hist) {
         std::cout << "--host-hist reads per-sample efficiencies of one GPU: not available with a GPU list" << std::endl;
@@ -252,6 +256,7 @@ int main(int argc, char* argv[])
     worker.epoch_from_idx = epoch_from_idx;
     gpuWorker gpuworker(&pdamc, streamNum, &SgDivSr, fretHistNum, _m, _cv, dataready, s_n, params, ga_start, ga_stop,
                         N, debuglevel);
+    gpuworker.set_coalesce(coalesce);
     pdamc.get_max_conversion_capacity();
     std::cout << "workers created\n";
     std::vector<std::thread> threads;

@@ -59,6 +59,7 @@ class mc {
         int fret_hist_num = 200;   // cmdline.ggo:14
         int left_pad = 2;          // main.cpp:155
         int max_batch = 1;         // most vectors per launch when the `mc` spans GPUs (sizes the exchange)
+        int carriers = 0;          // extra stream slots that carry coalesced launches (run_coalesced); needs !keep_mce
     };
 
     int devid;
@@ -88,7 +89,7 @@ class mc {
                                (opt.timing ? 0u : GSM_NO_TIMING) | (opt.peer_shared_device ? GSM_PEER_SHARED_DEVICE : 0u);
         for (size_t r = 0; r < ids.size(); ++r) {
             gsm_ctx* c = nullptr;
-            int rc = gsm_create(ids[r], _streamNum, flags, &c);
+            int rc = gsm_create(ids[r], _streamNum + (opt.keep_mce ? 0 : opt.carriers), flags, &c);
             if (rc == GSM_EINVAL && r == 0) {  // "gpu id set error!" (mc.cu:228-231): the reference returns quietly
                 std::printf("gpu id set error!\n");
                 workerNum.store(_streamNum);
@@ -101,7 +102,8 @@ class mc {
             GSM_CHECK_RETURN(gsm_set_resample_times(c, reSampleTimes));
         }
         ctx = part_[0];
-        streamNum = gsm_stream_count(ctx);
+        carriers_ = opt.keep_mce ? 0 : opt.carriers;
+        streamNum = gsm_stream_count(ctx) - carriers_;   // the carrier slots are not streams of the node
         workerNum.store(streamNum);
         // the reference keeps the 16 raw bytes of the device uuid in gpuuuid (mc.cu:43-48); the C
         // ABI hands out 32 hex digits
@@ -321,6 +323,40 @@ class mc {
         if (!bad_[sid]) batch_args_[sid] = args;
         return !bad_[sid];
     }
+    // The single vectors of the streams `sids` (args: their n*n + n values back to back, in the same
+    // order) in ONE launch on carrier slot `carrier` (0 .. carriers()-1).  Every vector is drawn with
+    // its own stream's epoch, so the results equal the per-stream launches bit for bit; afterwards
+    // streamQuery(sid) / hChi2(sid) / hHist(sid) of a member read its share of the carrier, until the
+    // stream runs by itself again.  A carrier is free again once carrierQuery says so AND its members
+    // have read their results.  Lifts the per-launch driver cost off a node that evaluates many small
+    // jobs (the reference's gpuWorker: one launch per stream, gpuWorker.cpp:38-87).
+    int carriers() const { return carriers_; }
+    bool run_coalesced(int carrier, int n, int N, const std::vector<int>& sids, const std::vector<float>& args)
+    {
+        const int P = (int)sids.size();
+        if (carrier < 0 || carrier >= carriers_ || P < 1 || n < 2 || (long long)args.size() != (long long)P * (n * n + n) ||
+            (part_.size() > 1 && P > opt_.max_batch))
+            return false;
+        for (size_t r = 0; r < part_.size(); ++r) {
+            int Nr = N;
+            if (part_.size() > 1) {
+                int64_t in_part = (int64_t)N - cuts_[r];
+                const int64_t size = cuts_[r + 1] - cuts_[r];
+                Nr = (int)(in_part < 0 ? 0 : (in_part > size ? size : in_part));
+            }
+            const int rc = gsm_run_coalesced(part_[r], Nr, streamNum + carrier, n, P, args.data(), sids.data());
+            if (rc == GSM_EINVAL && r == 0) return false;   // a vector the library refuses: nothing was launched
+            GSM_CHECK_RETURN(rc);
+        }
+        for (int sid : sids) { bad_[(size_t)sid] = 0; batch_[(size_t)sid] = 0; s_n[sid] = n; }
+        return true;
+    }
+    bool carrierQuery(int carrier)
+    {
+        bool done = true;
+        for (gsm_ctx* c : part_) done = (gsm_query(c, streamNum + carrier) == 1) && done;
+        return done;
+    }
     // draws of the next evaluation on the slot are keyed by `epoch` (reproducible runs)
     void set_epoch(int sid, uint32_t epoch)
     {
@@ -360,6 +396,7 @@ class mc {
     Options opt_;
     std::vector<gsm_ctx*> part_;
     std::vector<int64_t> cuts_;
+    int carriers_ = 0;
     std::vector<char> bad_;
     std::vector<int> batch_;
     std::vector<std::vector<float>> batch_args_;

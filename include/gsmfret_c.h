@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define GSM_ABI_VERSION 2
+#define GSM_ABI_VERSION 3
 
 #define GSM_OK 0
 #define GSM_EINVAL (-1)    /* bad argument */
@@ -144,6 +144,16 @@ int gsm_run(gsm_ctx* ctx, int N, int sid);
 /* batch entry: P parameter vectors of n states in one launch (args = P rows of n*n+n floats);
  * vector p draws with epoch + p.  Results via gsm_result_chi2v / gsm_result_histv. */
 int gsm_run_batch(gsm_ctx* ctx, int N, int sid, int n, int P, const float* args);
+/* The single vectors of several stream slots in ONE launch on a carrier slot (not in the reference:
+ * its gpuWorker issues one launch per stream, gpuWorker.cpp:38-87, which bounds a node at the
+ * reference's own job size by the driver calls of the issuing thread).  args = P rows of n*n+n
+ * floats, member_sids[p] = the stream vector p belongs to.  Vector p is drawn with member p's own
+ * epoch — the results are the bits the member's own gsm_run would have produced — and that epoch
+ * advances by one.  Until a member runs by itself again, gsm_query / gsm_sync / gsm_result_chi2 /
+ * gsm_result_hist(…, 0) / gsm_result_flags on the MEMBER read vector p of the carrier.  The carrier
+ * must not be a member and must not be launched again before the members' results have been read.
+ * Not with GSM_KEEP_MCE / GSM_KEEP_COUNTS (per-sample outputs are kept per stream). */
+int gsm_run_coalesced(gsm_ctx* ctx, int N, int carrier_sid, int n, int P, const float* args, const int* member_sids);
 /* same, the vectors of the previous gsm_run_batch / gsm_set_params stay resident: only launches */
 int gsm_run_resident(gsm_ctx* ctx, int N, int sid);
 /* mc::streamQuery(sid)   mc.cu:665-672 : 1 finished, 0 still running, <0 error */

@@ -28,7 +28,9 @@ def test_library_exports_every_declared_symbol(gsm):
     lib = gsm.load()
     missing = [s for s in header_symbols() if not hasattr(lib, s)]
     assert not missing, missing
-    assert lib.gsm_abi_version() == 1
+    import re
+    declared = int(re.search(r"#define\s+GSM_ABI_VERSION\s+(\d+)", open(os.path.join(ROOT, "include", "gsmfret_c.h")).read()).group(1))
+    assert lib.gsm_abi_version() == declared >= 3     # 2: exchange stamps + shared-device flag, 3: gsm_run_coalesced
 
 
 def test_python_binding_types_every_symbol(gsm):

@@ -264,3 +264,42 @@ def test_full_size_properties(gsm, oracle, cfg):
             mc.init_bursts(b.slice(b0, b1), g_offset=b0)
             hs += mc.evaluate(n, w.args[0], epoch=5)[1]
     assert np.array_equal(hs, h1)
+
+
+def test_coalesced_launch_equals_per_stream_launches(gsm, oracle):
+    """gsm_run_coalesced: the vectors of several streams in one launch on a carrier slot, every
+    vector with its own stream's epoch: each member then reads the bits its own launch would have
+    produced; its epoch advanced by one; the next run of the member on its own slot is its own again."""
+    w = synth.workload(4, n_bursts=900, R=8, P=5)
+    b = w.bursts()
+    ohist = oracle.observed_hist(b, NB)
+    with gsm.Mc(0, 8) as mc:
+        mc.set_reSampleTimes(8); mc.set_seed(5); mc.set_hist(NB, LEFT_PAD)
+        mc.init_bursts(b)
+        members = [1, 4, 2, 6, 0]
+        for k, sid in enumerate(members):
+            mc.set_epoch(sid, 100 * (k + 1))
+        mc.run_coalesced(b.n_bursts, 7, 2, w.args, members)
+        for k, sid in enumerate(members):
+            while not mc.streamQuery(sid):
+                pass
+            c, h = oracle.eval_chi2(b, 2, w.args[k], 8, 5, 100 * (k + 1), ohist, NB, LEFT_PAD)
+            assert np.array_equal(mc.hist(sid, 0), h)
+            assert bits(np.float32(mc.chi2(sid))) == bits(np.float32(c))
+            assert mc.chi2v(sid).shape == (1,)
+            with pytest.raises(gsm.GsmError):
+                mc.hist(sid, 1)                      # a member owns one vector of the carrier
+        # the members' epochs moved on by one: the next run of a member is its own launch again
+        c2, h2 = mc.evaluate(2, w.args[0], sid=4)
+        co, ho = oracle.eval_chi2(b, 2, w.args[0], 8, 5, 201, ohist, NB, LEFT_PAD)
+        assert np.array_equal(h2, ho) and bits(np.float32(c2)) == bits(np.float32(co))
+        # refusals: the carrier among the members, a member twice
+        with pytest.raises(gsm.GsmError):
+            mc.run_coalesced(b.n_bursts, 7, 2, w.args[:2], [7, 1])
+        with pytest.raises(gsm.GsmError):
+            mc.run_coalesced(b.n_bursts, 7, 2, w.args[:2], [1, 1])
+    with gsm.Mc(0, 3, keep_mce=True) as mc:
+        mc.set_reSampleTimes(8); mc.set_hist(NB, LEFT_PAD)
+        mc.init_bursts(b)
+        with pytest.raises(gsm.GsmError):
+            mc.run_coalesced(b.n_bursts, 2, 2, w.args[:2], [0, 1])   # per-sample outputs are per stream

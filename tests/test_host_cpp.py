@@ -61,19 +61,19 @@ def test_reference_gpuworker_compiles_unchanged_against_the_shim():
     assert r.returncode == 2 and "usage" in r.stderr
 
 
-def _check_node_output(oracle, exe, tmp_path, streams):
-    w = synth.workload(4, n_bursts=1200, R=8, P=10)
+def _check_node_output(oracle, exe, tmp_path, streams, coalesce=0, P=10):
+    w = synth.workload(4, n_bursts=1200, R=8, P=P)
     b = w.bursts()
     synth.save_bin(b, str(tmp_path / "b.bin"))
     with open(tmp_path / "p.txt", "w") as f:
         for a in w.args:
             f.write("2 " + " ".join(repr(float(x)) for x in a) + "\n")
         f.write("3 " + " ".join(repr(float(x)) for x in synth.workload(3).args[0]) + "\n")   # n changes mid-run
-    r = subprocess.run([exe, str(tmp_path / "b.bin"), str(tmp_path / "p.txt"), str(tmp_path / "o.txt"), str(streams), "8", "42"],
-                       capture_output=True, text=True, timeout=120)
+    r = subprocess.run([exe, str(tmp_path / "b.bin"), str(tmp_path / "p.txt"), str(tmp_path / "o.txt"), str(streams), "8", "42"]
+                       + ([str(coalesce)] if coalesce else []), capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stderr
     rows = [l.split() for l in open(tmp_path / "o.txt") if l.strip()]
-    assert len(rows) == 11
+    assert len(rows) == P + 1
     ohist = oracle.observed_hist(b, NB)
     allargs = [(2, a) for a in w.args] + [(3, synth.workload(3).args[0])]
     for row in rows:
@@ -94,6 +94,16 @@ def test_reference_gpuworker_drives_the_library(oracle, tmp_path):
     same results as the oracle, bit for bit, through set_nstates / set_params / setBurstBd /
     init_randstate / set_params_buff / run_kernel / streamQuery as the reference issues them."""
     _check_node_output(oracle, DROPIN, tmp_path, 3)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("streams,coalesce", [(8, 2), (16, 1), (3, 3)])
+def test_local_node_coalesced_launches_match_oracle(oracle, tmp_path, streams, coalesce):
+    """gpuWorker::set_coalesce: vectors that are ready together ride ONE launch on a carrier slot
+    (gsm_run_coalesced), each with its own stream's draw epoch — the node's output is the oracle's,
+    bit for bit, like the one-launch-per-stream node's (the vector of another model in the list is
+    launched on its own)."""
+    _check_node_output(oracle, build(), tmp_path, streams, coalesce=coalesce, P=60)
 
 
 @pytest.mark.gpu

@@ -10,7 +10,7 @@ for job in "$@"; do
       timeout 1500 python -m pytest tests -m gpu -x -q > $O/${T}_gpu_tests.log 2>&1; echo "tests rc=$? $(tail -1 $O/${T}_gpu_tests.log)";;
     bench)
       M=${a2:-replay}
-      timeout 600 python bench.py --cfg $a1 --mode $M --no-cpu $a3 > $O/${T}_bench_cfg${a1}_$M.json 2> $O/${T}_bench_cfg${a1}_$M.err; echo "bench cfg$a1 $M rc=$?"
+      timeout 600 python bench.py --cfg $a1 --only main --mode $M --no-cpu $a3 > $O/${T}_bench_cfg${a1}_$M.json 2> $O/${T}_bench_cfg${a1}_$M.err; echo "bench cfg$a1 $M rc=$?"
       python - <<PY
 import json
 try:
@@ -23,7 +23,7 @@ PY
       timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${T}_launches.csv python bench.py --steps 20 --warmup 3 --no-cpu > $O/${T}_ncu_list.log 2>&1; echo "ncu list rc=$?";;
     ncu)
       M=${a2:-replay}; B=""; [ -n "$a3" ] && B="--bursts $a3"
-      timeout 900 ncu --set full --clock-control none --import-source on -k regex:pda_eval -s 3 -c 1 -o $O/${T}_full_cfg${a1}_$M -f python bench.py --cfg $a1 $B --steps 3 --warmup 3 --no-cpu --mode $M > $O/${T}_ncu_full_cfg${a1}_$M.log 2>&1; echo "ncu cfg$a1 $M rc=$?";;
+      timeout 900 ncu --set full --clock-control none --import-source on -k regex:pda_eval -s 3 -c 1 -o $O/${T}_full_cfg${a1}_$M -f python bench.py --cfg $a1 --only main $B --steps 3 --warmup 3 --no-cpu --mode $M > $O/${T}_ncu_full_cfg${a1}_$M.log 2>&1; echo "ncu cfg$a1 $M rc=$?";;
     variants)
       bash tools/variant_bench.sh --cfg $a1 --steps 100 --warmup 5 $a3 -- $(echo $a2 | tr ',' ' ') | tee -a $O/${T}_variants_cfg$a1.txt;;
     *) echo "unknown job $job";;

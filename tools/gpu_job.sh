@@ -1,13 +1,7 @@
 #!/bin/bash
 # scratch job for one gpurun call (rewritten per call; tools/gpu.sh holds the reusable jobs)
-O=gpurun_out; T=${TAG:-r02j}; mkdir -p $O
-./tools/log2_probe.bin > $O/${T}_log2_probe.txt 2>&1; cat $O/${T}_log2_probe.txt | grep -c "off by one"
-timeout 1700 python -m pytest tests -m gpu -x -q > $O/${T}_gpu_tests.log 2>&1; echo "tests rc=$? $(tail -1 $O/${T}_gpu_tests.log)"
-timeout 900 python bench.py > $O/${T}_bench_default.json 2> $O/${T}_bench_default.err; echo "bench rc=$?"; tail -8 $O/${T}_bench_default.err
-python - <<PY
-import json
-d=json.loads(open('$O/${T}_bench_default.json').read().strip().splitlines()[-1])
-print('main %.4g ms %.4f e2e %.4g frac %.3f' % (d['value'], d['ms_per_step'], d['e2e']['value'], d['roofline']['frac']))
-for k,v in d.get('configs',{}).items(): print(k, '%.4g ms %.4f e2e %.4g pe/s %.4g frac %.3f' % (v['value'], v['ms_per_step'], v['e2e']['value'], v['param_evals_per_s'], v['roofline']['frac']))
-print(json.dumps(d.get('cpu_baseline'))[:3000])
-PY
+O=gpurun_out; T=${TAG:-r02k}; mkdir -p $O
+timeout 1500 python -m pytest tests -m gpu -x -q > $O/${T}_gpu_tests.log 2>&1; echo "tests rc=$? $(tail -1 $O/${T}_gpu_tests.log)"
+V="variants/libgsmfret_base.so default variants/libgsmfret_t8.so variants/libgsmfret_t16.so variants/libgsmfret_t24.so variants/libgsmfret_d12m3.so variants/libgsmfret_d6.so"
+for c in 2 3; do echo "== cfg $c"; bash tools/variant_bench.sh --cfg $c --only main --steps 100 --warmup 5 -- $V; done 2>&1 | tee $O/${T}_variants.txt
+echo "== cfg 5 (1.25e6)"; bash tools/variant_bench.sh --cfg 5 --bursts 1250000 --steps 50 --warmup 5 -- $V 2>&1 | tee -a $O/${T}_variants.txt
