@@ -72,13 +72,27 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)", 1965.0
 
 
-def ncu_entry(workload: str, mode: str):
-    """What the committed ncu capture of this workload's evaluation kernel says (profiles/ncu_traffic.json)."""
+def ncu_entry(workload: str, mode: str, bursts: int):
+    """What the committed ncu capture of this workload's evaluation kernel says per launch
+    (profiles/ncu_traffic.json): the entry for exactly this many bursts per GPU, else the one of the
+    workload's nominal size when that is what runs."""
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-            return json.load(f).get(f"{workload}/{mode}")
+            d = json.load(f)
+        e = d.get(f"{workload}/{mode}@{int(bursts)}")
+        if e is None and synth_nominal_bursts(workload) == int(bursts):
+            e = d.get(f"{workload}/{mode}")
+        return e
     except Exception:   # noqa: BLE001
         return None
+
+
+def synth_nominal_bursts(workload: str):
+    for c in (1, 2, 3, 4, 5):
+        w = synth.workload(c)
+        if w.name == workload:
+            return w.n_bursts
+    return None
 
 
 class ClockSampler:
@@ -562,7 +576,7 @@ def time_leg(env, cfg, w, b, kind, steps, warmup, mode, collective, g_offset=0, 
     value = samples_job * steps / (dev_ms * 1e-3)
     algo_bytes = b.algorithmic_bytes() + (612 * P_local if population else 0)
     hbm_achieved = algo_bytes / (float(per_rank[0, 0]) * 1e-3) / 1e9
-    ent = ncu_entry(w.name, mode) if (env.args.bursts is None and env.args.repeats is None) else None
+    ent = ncu_entry(w.name, mode, B) if env.args.repeats is None else None
     f_clk = (clk.get("sm_mhz") or sm_max) * 1e6
     issue_peak = 148 * 128 * f_clk
     per_gpu = value / world

@@ -28,28 +28,6 @@ constexpr int kChunkMax = PDA_CHUNK_MAX;  // most consecutive samples a warp dra
 constexpr int kMaxBins = 1024;          // nb + 2 <= kMaxBins
 constexpr uint32_t kStepCap = 1u << 20; // guards the GPU against rates <= 0 (a hang in the reference)
 
-// Replay mode defers the FP64 binomial draws: the walk of a lane only RECORDS them (one 16-byte
-// entry per draw in a lane-private queue in shared memory) and the warp works the queues off
-// together every few trips — the exp/log start values of all recorded draws packed 32 to a
-// warp-instruction, then the inversion loops of all lanes merged into one loop.  The draws of a
-// sample stay in order on the sample's own xor128 stream, so the results are the same bits.
-#ifndef PDA_FIFO_D
-#define PDA_FIFO_D 8
-#endif
-#ifndef PDA_FETCH_TH
-#define PDA_FETCH_TH 12
-#endif
-constexpr int kFifoD = PDA_FIFO_D;       // entries per lane (a trip adds at most 3: start, draw, end)
-constexpr int kFetchTh = PDA_FETCH_TH;   // lanes that must be waiting before the merged loop stops to fetch
-constexpr uint32_t kEntDraw = 0u, kEntStart = 1u, kEntEnd = 2u;
-#ifdef PDA_NO_DEFER
-constexpr bool kDeferDraws = false;      // A/B builds: every draw taken where it arises, as before
-#else
-constexpr bool kDeferDraws = true;
-#endif
-template <int kMode> struct Defers { static constexpr bool value = kDeferDraws && kMode == kModeReplay; };
-static_assert(kFifoD >= 5 && kFifoD <= 17, "two kind bits per entry live in one 32-bit register");
-
 // parameter vector staged in shared memory, with the per-state terms hoisted
 struct SmemParams {
     int n;
@@ -266,8 +244,7 @@ __device__ __forceinline__ void lane_begin(Lane& L, const SmemParams& sp, const 
         L.xs.s0 = xs.x; L.xs.s1 = xs.y; L.xs.s2 = xs.z; L.xs.s3 = xs.w;
     }
     // replay mode: the xor128 stream of the sample is seeded from its step-0 block (lane_step)
-    L.F = 0.0f; L.spent = 0.0f;
-    if (!Defers<kMode>::value) L.acc = 0.0f;   // deferred draws: the queue's start entry resets it (the consumer owns acc and xs)
+    L.F = 0.0f; L.acc = 0.0f; L.spent = 0.0f;
     L.fb = (float)L.start;
     L.first = 0;
     L.step = 0;
@@ -282,12 +259,9 @@ __device__ __forceinline__ void lane_save_reference(const Lane& L, const EvalArg
 }
 
 // one dwell window (one trip of the reference's while loop, mc.cu:117-191)
-// Replay mode returns the binomial draw of the window instead of taking it: has_draw, (draw_n, draw_p),
-// and at step 0 the seed of the sample's xor128 stream.
 template <int kLayout, bool kBg, int kMode>
 __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const EvalArgs& a, uint32_t epoch,
-                                          const double2* __restrict__ ltab, const double* __restrict__ rcp,
-                                          uint32_t& seed_out, bool& has_draw, int& draw_n, float& draw_p)
+                                          const double2* __restrict__ ltab, const double* __restrict__ rcp)
 {
     constexpr bool kFast = kMode == kModeNormal;
     constexpr bool kSobol = kMode == kModeReference;
@@ -314,8 +288,7 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
         if (kFast) iw = (w.x & 0xffu) | ((w.y & 0xffu) << 8) | ((w.z & 0xffu) << 16) | (w.w << 24);
         else if (!kSobol) {
             iw = ((w.x & 0xffu) << 24) | ((w.y & 0xffu) << 16) | ((w.z & 0xffu) << 8) | 0x80u;
-            if (Defers<kMode>::value) seed_out = w.w;
-            else L.xs.seed((uint64_t)w.w);
+            L.xs.seed((uint64_t)w.w);
         }
         L.si = pick(sp.cumP, n, u01(iw));
     }
@@ -410,16 +383,10 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
             if (kSobol) w.z = (uint32_t)(sobol_next(L) >> 32);
             const float rd = det_norm_icdf(w.z) * sp.v[si] + sp.rootE[si];
             const float de = 1.0f / (1.0f + det_pow6f(rd / kR0));
-            if (Defers<kMode>::value) {
-                has_draw = true;
-                draw_n = (int)f_i;
-                draw_p = de;
-            } else {
-                ai = (int)binomial(L.xs, (int)f_i, (double)de, ltab);
-            }
+            ai = (int)binomial(L.xs, (int)f_i, (double)de, ltab);
         }
     }
-    if (!Defers<kMode>::value) L.acc += (float)ai;
+    L.acc += (float)ai;
     L.si = sj;
     L.step++;
 }
@@ -585,179 +552,6 @@ __device__ __forceinline__ void peer_exchange_block(const EvalArgs& a, unsigned 
     __syncthreads();
 }
 
-// Dynamic shared memory of the evaluation kernel: per-warp histograms, then (deferred draws) per warp
-// kFifoD rows of 32 16-byte queue entries — row 0 holds the lanes' xor128 streams, rows 1.. the
-// entries, entry e of lane l at [(1 + e) * 32 + l] (conflict-free) — the list of the entries that are
-// draws (2 B each, filled in arrival order, read 32 at a time), and the lanes' acceptor sums.
-struct QueueView {
-    unsigned int* hist;        // this warp's histogram
-    uint4* state;              // [32] xor128 stream of each lane's consumer
-    uint4* fifo;               // [(kFifoD - 1) * 32]
-    unsigned short* drawref;   // [(kFifoD - 1) * 32]
-    float* acc;                // [32]
-};
-constexpr int kFifoCap = kFifoD - 1;   // entries a lane can hold
-__device__ __forceinline__ QueueView queue_view(int nb)
-{
-    extern __shared__ __align__(16) unsigned int s_dyn[];
-    constexpr int kWarps = kBlock / 32;
-    const int wid = threadIdx.x >> 5;
-    const int nbp = nb + 2;
-    uint4* q0 = reinterpret_cast<uint4*>(s_dyn + ((kWarps * nbp + 3) & ~3));
-    unsigned short* d0 = reinterpret_cast<unsigned short*>(q0 + kWarps * (kFifoD * 32));
-    float* a0 = reinterpret_cast<float*>(d0 + kWarps * (kFifoD * 32));
-    QueueView v;
-    v.hist = s_dyn + wid * nbp;
-    v.state = q0 + wid * (kFifoD * 32);
-    v.fifo = v.state + 32;
-    v.drawref = d0 + wid * (kFifoD * 32);
-    v.acc = a0 + wid * 32;
-    return v;
-}
-
-// Deferred draws: work the draw queues of one warp off (called by all 32 lanes).  A call, not
-// inlined: the merged loop below needs most of the register file, and this way the walk state of
-// the lanes is parked once per call instead of the loop's variables being spilled on every trip;
-// for the same reason the consumer state of a lane (the xor128 stream and the acceptor sum of the
-// sample its queue is in the middle of) lives in shared memory, not in registers of the walk.
-static __device__ __noinline__ void drain_draw_queues(const EvalArgs& a, const double2* __restrict__ ltab, int q_cnt,
-                                                      uint32_t q_kinds, int w_draws)
-{
-    const int lane = threadIdx.x & 31;
-    const QueueView v = queue_view(a.nb);
-    // pass 1: q^n = exp(n log(1 - p)) of every recorded draw that the inversion will take,
-    // the draws of all lanes dealt 32 at a time (no order among them: nothing is drawn yet)
-    for (int k = lane; k < w_draws; k += 32) {
-        uint4* ent = v.fifo + v.drawref[k];
-        const int n = (int)ent->x;
-        const double p = (double)__uint_as_float(ent->y);
-        const bool no_trials = n <= 0 && n >= -64 && p > 0.0 && p < 1.0;
-        const double pp = !(p <= 0.5) ? 1.0 - p : p;
-        if (!no_trials && pp * (double)n <= 30.0) {
-            const double qn = det_exp((double)n * det_log(1.0 - pp, ltab));
-            ent->z = (uint32_t)__double2loint(qn);
-            ent->w = (uint32_t)__double2hiint(qn);
-        }
-    }
-    __syncwarp();
-    // pass 2: every lane walks its own queue in order on the sample's xor128 stream; the
-    // inversion loops (role of rk_binomial_inversion, binom.cuh:135-169) of the lanes are ONE
-    // loop, a lane that finishes a draw waits until enough others have to fetch the next
-    const bool keep_samples = a.mcE || a.sum_ai || a.n_steps;
-    int rd = 0;
-    bool have = false, mir = false, cold = false;
-    int n = 0, X = 0, bound = 0;
-    double pp = 0.0, px = 1.0, U = 0.0, dX = 0.0, dn1 = 1.0;
-    for (;;) {
-        for (;;) {
-            const unsigned idle = __ballot_sync(0xffffffffu, !have && !cold && rd < q_cnt);
-            const unsigned busy = __ballot_sync(0xffffffffu, have);
-            if ((idle | busy) == 0u) break;
-            if (idle != 0u && (busy == 0u || __popc(idle) >= kFetchTh)) {
-                if (!have && !cold) {
-                    while (rd < q_cnt) {
-                        const uint4 ent = v.fifo[rd * 32 + lane];
-                        const uint32_t kind = (q_kinds >> (2 * rd)) & 3u;
-                        ++rd;
-                        if (kind == kEntStart) {
-                            Xor128 xs;
-                            xs.seed((uint64_t)ent.y);   // role of setup_kernel's rk_seed, gen_rand.cuh:19-21
-                            v.state[lane] = make_uint4(xs.s0, xs.s1, xs.s2, xs.s3);
-                            v.acc[lane] = 0.0f;
-                        } else if (kind == kEntEnd) {
-                            // IEEE division in both modes: E takes few distinct values (small integer
-                            // counts), so a 1-ulp difference would move whole atoms of the distribution.
-                            // 0 / F = +0 is spelled out: a zero numerator sends the division through its slow path.
-                            const float F = __uint_as_float(ent.y);
-                            const float acc = v.acc[lane];
-                            const float e = (F > 0.0f && acc != 0.0f) ? __fdiv_rn(acc, F) : 0.0f;
-                            if (keep_samples) {
-                                const size_t oi = ((size_t)ent.w << 32) | (size_t)ent.z;
-                                if (a.mcE) a.mcE[oi] = e;
-                                if (a.sum_ai) a.sum_ai[oi] = (long long)acc;   // integer-valued, exact below 2^24
-                                if (a.n_steps) a.n_steps[oi] = (int32_t)ent.x;
-                            }
-                            const int bin = hist_index(e, a.nb);
-                            const unsigned fm = __activemask();
-                            const unsigned peers = __match_any_sync(fm, bin);
-                            if (lane == __ffs(peers) - 1) atomicAdd(&v.hist[bin], (unsigned)__popc(peers));
-                        } else {
-                            // the cases of binomial() (pda_device.cuh), in its order
-                            n = (int)ent.x;
-                            const double p = (double)__uint_as_float(ent.y);
-                            if (n <= 0 && n >= -64 && p > 0.0 && p < 1.0) {
-                                const uint4 st = v.state[lane];
-                                Xor128 xs{st.x, st.y, st.z, st.w};
-                                xs.next();
-                                xs.next();
-                                v.state[lane] = make_uint4(xs.s0, xs.s1, xs.s2, xs.s3);
-                                if (!(p <= 0.5)) v.acc[lane] += (float)n;
-                                continue;
-                            }
-                            mir = !(p <= 0.5);
-                            pp = mir ? 1.0 - p : p;
-                            if (pp * (double)n <= 30.0) {
-                                bound = n;
-                                if (n < 1 || n > 10) {
-                                    const double np = (double)n * pp;
-                                    double bd = np + 10.0 * __dsqrt_rn(np * (1.0 - pp) + 1.0);
-                                    if (!(bd <= (double)n)) bd = (double)n;
-                                    bound = (int)bd;
-                                }
-                                X = 0;
-                                dX = 0.0;
-                                dn1 = (double)n + 1.0;
-                                px = __hiloint2double((int)ent.w, (int)ent.z);   // q^n from pass 1
-                                const uint4 st = v.state[lane];
-                                Xor128 xs{st.x, st.y, st.z, st.w};
-                                U = xs.next_double();
-                                v.state[lane] = make_uint4(xs.s0, xs.s1, xs.s2, xs.s3);
-                                have = true;
-                            } else {
-                                cold = true;   // BTPE: taken below, outside the merged loop
-                            }
-                            break;
-                        }
-                    }
-                }
-            }
-            if (have) {
-                if (U > px) {
-                    X++;
-                    dX += 1.0;
-                    if (X > bound) {   // start over with a fresh uniform (binom.cuh:157-161); q^n is still in the entry
-                        const uint4 ent = v.fifo[(rd - 1) * 32 + lane];
-                        X = 0;
-                        dX = 0.0;
-                        px = __hiloint2double((int)ent.w, (int)ent.z);
-                        const uint4 st = v.state[lane];
-                        Xor128 xs{st.x, st.y, st.z, st.w};
-                        U = xs.next_double();
-                        v.state[lane] = make_uint4(xs.s0, xs.s1, xs.s2, xs.s3);
-                    } else {
-                        U -= px;
-                        px = ((dn1 - dX) * pp * px) / (dX * (1.0 - pp));
-                    }
-                } else {
-                    v.acc[lane] += (float)(mir ? n - X : X);
-                    have = false;
-                }
-            }
-        }
-        have = false;   // (it is: no lane was busy) — nothing of the inversion lives across the call below
-        if (!__any_sync(0xffffffffu, cold)) break;
-        if (cold) {
-            const uint4 st = v.state[lane];
-            Xor128 t{st.x, st.y, st.z, st.w};
-            const long long Xb = binomial_btpe(t, n, pp);
-            v.state[lane] = make_uint4(t.s0, t.s1, t.s2, t.s3);
-            v.acc[lane] += (float)(int)(mir ? (long long)n - Xb : Xb);
-            cold = false;
-        }
-    }
-    __syncwarp();
-}
-
 // Persistent, warp-autonomous evaluation kernel.
 //   kLayout 0: raw int64 burst_ad/burst_dd (fallback), 1: packed words scanned photon by
 //   photon, 2: packed words + running-max / next-photon index (O(log ph) windows).
@@ -793,8 +587,6 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
     const int nbp = a.nb + 2;
     SmemParams& sp = s_params[wid];
     unsigned int* hist = s_hist_all + wid * nbp;
-    constexpr bool kDefer = Defers<kMode>::value;
-    const QueueView qv = queue_view(a.nb);   // pointers are only used in deferred mode
 
     const int64_t per_p = a.N * (int64_t)a.R;  // samples per parameter vector
     const unsigned long long chunks_per_p = (unsigned long long)((per_p + a.chunk - 1) >> a.chunk_log2);
@@ -819,14 +611,8 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
 
     Lane L;
     bool active = false;
-    // queue state (replay mode): entries of this lane, their kinds (2 bits each), draws of the warp
-    int q_cnt = 0;
-    uint32_t q_kinds = 0u;
-    int w_draws = 0;
-    const bool keep_samples = a.mcE || a.sum_ai || a.n_steps;
 
     for (;;) {
-        bool drain = false;
         // ---- hand samples to idle lanes -------------------------------------------------
         for (;;) {
             const unsigned need = __ballot_sync(0xffffffffu, !active);
@@ -852,13 +638,10 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
                 const int p = small ? (int)((uint32_t)item / (uint32_t)chunks_per_p) : (int)(item / chunks_per_p);
                 const int cur_p = wc.cur_p;
                 if (p != cur_p) {
-                    // the samples still in the queues belong to the histogram of the previous vector
-                    const bool queued = kDefer && __any_sync(0xffffffffu, q_cnt > 0);
-                    if (need != 0xffffffffu || queued) {   // park the chunk until every lane has drained
+                    if (need != 0xffffffffu) {   // park the chunk until every lane has drained
                         __syncwarp();
                         if (lane == 0) { wc.have_pending = 1; wc.pend_item = item; }
                         __syncwarp();
-                        drain = queued;
                         break;
                     }
                     // all lanes idle: switch vector
@@ -927,48 +710,27 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
                 active = false;
             }
         }
-        const bool none_active = __ballot_sync(0xffffffffu, active) == 0u;
-
-        // ---- replay mode: work the draw queues off -----------------------------------------
-        // when a queue could overflow in the coming trip, before the histogram changes hands, and
-        // when the warp has nothing else left
-        if (kDefer && (drain || none_active || __any_sync(0xffffffffu, q_cnt > kFifoCap - 3)) &&
-            __any_sync(0xffffffffu, q_cnt > 0)) {
-            // (a call, not inlined: the callee gets the whole register file for the merged loop, the
-            // walk state of the lanes is parked in local memory once per call instead of the loop's
-            // variables being spilled on every trip)
-            drain_draw_queues(a, s_logtab, q_cnt, q_kinds, w_draws);
-            q_cnt = 0;
-            q_kinds = 0u;
-            w_draws = 0;
-            __syncwarp();
-        }
-        if (none_active) {
+        if (__ballot_sync(0xffffffffu, active) == 0u) {
             if (wc.exhausted && !wc.have_pending) break;
             continue;
         }
 
         // ---- one dwell window for every active lane -------------------------------------
-        bool fin = false, has_draw = false;
-        const bool first_step = active && L.step == 0u;
-        uint32_t seed = 0u;
-        int draw_n = 0;
-        float draw_p = 0.0f;
         if (active) {
-            lane_step<kLayout, kBg, kMode>(L, sp, a, wc.epoch, s_logtab, s_rcp, seed, has_draw, draw_n, draw_p);
-            fin = !(L.T > L.spent);
+            lane_step<kLayout, kBg, kMode>(L, sp, a, wc.epoch, s_logtab, s_rcp);
+            bool fin = !(L.T > L.spent);
             if (!fin && L.step >= kStepCap) {
                 atomicOr(a.counters + 2, 1ull);
                 fin = true;
             }
-            if (fin && !kDefer) {
+            if (fin) {
                 if (kMode == kModeReference) lane_save_reference(L, a);
                 // IEEE division in both modes: E takes few distinct values (small integer
                 // counts), so a 1-ulp difference would move whole atoms of the distribution.
                 // 0 / F = +0 is spelled out: a zero numerator (no acceptor photon drawn — a
                 // large share of the samples) sends the division through its slow path.
                 const float e = (L.F > 0.0f && L.acc != 0.0f) ? __fdiv_rn(L.acc, L.F) : 0.0f;
-                if (keep_samples) {
+                if (a.mcE || a.sum_ai || a.n_steps) {
                     const size_t oi = (size_t)wc.cur_p * (size_t)per_p + (size_t)L.bl * (size_t)a.R + L.rep;
                     if (a.mcE) a.mcE[oi] = e;
                     if (a.sum_ai) a.sum_ai[oi] = (long long)L.acc;   // integer-valued, exact below 2^24
@@ -980,34 +742,10 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
                 const unsigned fm = __activemask();
                 const unsigned peers = __match_any_sync(fm, bin);
                 if (lane == __ffs(peers) - 1) atomicAdd(&hist[bin], (unsigned)__popc(peers));
+                active = false;
             }
-            if (fin) active = false;
         }
         __syncwarp();
-        if (kDefer) {
-            // record what the window left to do, in the order the sample needs it
-            if (first_step) {
-                qv.fifo[q_cnt * 32 + lane].y = seed;
-                q_kinds |= kEntStart << (2 * q_cnt);
-                ++q_cnt;
-            }
-            const unsigned dm = __ballot_sync(0xffffffffu, has_draw);
-            if (has_draw) {
-                const int at = q_cnt * 32 + lane;
-                qv.fifo[at].x = (uint32_t)draw_n;
-                qv.fifo[at].y = __float_as_uint(draw_p);
-                qv.drawref[w_draws + __popc(dm & lt_mask)] = (unsigned short)at;
-                ++q_cnt;                         // kEntDraw = 0: no kind bits to set
-            }
-            w_draws += __popc(dm);
-            if (fin) {
-                const size_t oi = (size_t)wc.cur_p * (size_t)per_p + (size_t)L.bl * (size_t)a.R + L.rep;
-                qv.fifo[q_cnt * 32 + lane] = make_uint4(L.step, __float_as_uint(L.F), (uint32_t)oi, (uint32_t)((unsigned long long)oi >> 32));
-                q_kinds |= kEntEnd << (2 * q_cnt);
-                ++q_cnt;
-            }
-            __syncwarp();
-        }
     }
     const int cur_p = wc.cur_p;
 
@@ -1053,31 +791,18 @@ template <int kLayout, bool kBg, int kMode>
 static int resident_blocks(size_t dyn)
 {
     int nb = 0;
-    // static + dynamic shared memory beyond 48 KB per block needs the opt-in; the value is a cap
-    cudaFuncAttributes fa{};
-    cudaFuncGetAttributes(&fa, pda_eval_kernel<kLayout, kBg, kMode>);
-    if (dyn + fa.sharedSizeBytes > 48 * 1024)
-        cudaFuncSetAttribute(pda_eval_kernel<kLayout, kBg, kMode>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)(dyn > 64 * 1024 ? dyn : 64 * 1024));
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, pda_eval_kernel<kLayout, kBg, kMode>, kBlock, dyn);
     return nb < 1 ? 1 : nb;
 }
 
-// per-warp histograms, and in replay mode the draw queues (16 B entries) and the list of draws (2 B)
-template <int kMode>
-static inline size_t eval_dyn_smem(int nb)
-{
-    const size_t hist_words = ((size_t)(kBlock / 32) * (size_t)(nb + 2) + 3) & ~(size_t)3;
-    const size_t queues = Defers<kMode>::value ? (size_t)(kBlock / 32) * kFifoD * 32 * (16 + 2) + kBlock * sizeof(float) : 0;
-    return hist_words * sizeof(unsigned int) + queues;
-}
+static inline size_t eval_dyn_smem(int nb) { return (size_t)(kBlock / 32) * (size_t)(nb + 2) * sizeof(unsigned int); }
 
 template <int kMode>
 static LaunchCfg eval_launch_cfg_t(int device, int layout, bool with_bg, int nb)
 {
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-    const size_t dyn = eval_dyn_smem<kMode>(nb);
+    const size_t dyn = eval_dyn_smem(nb);
     int per;
     if (layout == 0) per = with_bg ? resident_blocks<0, true, kMode>(dyn) : resident_blocks<0, false, kMode>(dyn);
     else if (layout == 1) per = with_bg ? resident_blocks<1, true, kMode>(dyn) : resident_blocks<1, false, kMode>(dyn);
@@ -1112,7 +837,7 @@ static cudaError_t launch_eval_t(const EvalArgs& a_in, int layout, bool with_bg,
     if (a_in.nb + 2 > kMaxBins) return cudaErrorInvalidValue;
     EvalArgs a = a_in;
     shape_launch(a, cfg);
-    const size_t dyn = eval_dyn_smem<kMode>(a.nb);
+    const size_t dyn = eval_dyn_smem(a.nb);
 #define PDA_LAUNCH(LAY, BG) pda_eval_kernel<LAY, BG, kMode><<<cfg.grid, cfg.block, dyn, s>>>(a)
     if (layout == 0) { if (with_bg) PDA_LAUNCH(0, true); else PDA_LAUNCH(0, false); }
     else if (layout == 1) { if (with_bg) PDA_LAUNCH(1, true); else PDA_LAUNCH(1, false); }

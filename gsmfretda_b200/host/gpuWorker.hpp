@@ -24,7 +24,19 @@ class gpuWorker {
     // the same model over the same burst range at the same moment, they are evaluated by ONE launch
     // on a carrier slot of the `mc` (mc::run_coalesced; every vector keeps its own stream's draw
     // epoch, so the results are the bits of the per-stream launches).  0 switches it off.
-    void set_coalesce(int min_group) { coalesce_min = (pdamc->carriers() > 0) ? min_group : 0; }
+    // While other evaluations are still in flight, vectors that are ready wait up to `linger_us` for
+    // company (until `target` of them are ready): the launches a node saves this way are what bounds it
+    // at the reference's own job size (~9 us of driver calls per launch on the one gpuWorker thread).
+    void set_coalesce(int min_group, int target = 16, int linger_us = 0)
+    {
+        coalesce_min = (pdamc->carriers() > 0) ? min_group : 0;
+        coalesce_target = target;
+        coalesce_linger_us = linger_us;
+    }
+    // what the coalescing loop did: passes over the streams, launches that carried a group, vectors in
+    // those groups, launches of a single stream
+    struct Stats { unsigned long long passes = 0, group_launches = 0, grouped_vectors = 0, single_launches = 0; };
+    const Stats& stats() const { return stats_; }
 
     void run(int sz_burst)
     {
@@ -61,12 +73,18 @@ class gpuWorker {
         pdamc->set_gpuid();
         const int C = pdamc->carriers();
         std::vector<std::vector<int>> riding((size_t)C);
-        std::vector<int> seen((size_t)streamNum, -1), ready, group;
+        std::vector<int> seen((size_t)streamNum, -1), ready, group, on_carrier((size_t)streamNum, -1);
+        std::vector<char> landed((size_t)C, 0);
+        bool lingering = false;
+        std::chrono::steady_clock::time_point linger_since{};
         std::vector<std::unique_lock<std::mutex>> held;
         std::vector<float> args;
         do {
+            ++stats_.passes;
             ready.clear();
             held.clear();
+            // one query per carrier and pass answers for all its members
+            for (int c = 0; c < C; ++c) landed[(size_t)c] = !riding[(size_t)c].empty() && pdamc->carrierQuery(c);
             for (int sid = 0; sid < streamNum; ++sid) {
                 std::unique_lock<std::mutex> lck(_m[sid], std::defer_lock);
                 seen[(size_t)sid] = -1;
@@ -74,7 +92,8 @@ class gpuWorker {
                 const int st = dataready[sid];
                 seen[(size_t)sid] = st;
                 if (st == 3) {
-                    const bool done = pdamc->streamQuery(sid);
+                    const int c = on_carrier[(size_t)sid];
+                    const bool done = c >= 0 ? landed[(size_t)c] != 0 : pdamc->streamQuery(sid);
                     if (done) dataready[sid] = 4;
                     lck.unlock();
                     if (done) _cv[sid].notify_one();
@@ -83,8 +102,22 @@ class gpuWorker {
                     held.push_back(std::move(lck));
                 }
             }
+            // company is worth waiting for only while the GPU has other work
+            if (!ready.empty()) {
+                int inflight = 0;
+                for (int sid = 0; sid < streamNum; ++sid) inflight += seen[(size_t)sid] == 3;
+                const auto now = std::chrono::steady_clock::now();
+                if (!lingering) { lingering = true; linger_since = now; }
+                const bool wait_more = inflight > 0 && (int)ready.size() < coalesce_target &&
+                                       std::chrono::duration_cast<std::chrono::microseconds>(now - linger_since).count() < coalesce_linger_us;
+                if (wait_more) {
+                    held.clear();   // the vectors stay ready (state 2); look again
+                    continue;
+                }
+                lingering = false;
+            }
             for (int c = 0; c < C; ++c) {
-                if (riding[(size_t)c].empty() || !pdamc->carrierQuery(c)) continue;
+                if (riding[(size_t)c].empty() || !landed[(size_t)c]) continue;
                 bool read = true;
                 for (int sid : riding[(size_t)c]) read = read && seen[(size_t)sid] >= 0 && seen[(size_t)sid] != 3 && seen[(size_t)sid] != 4;
                 if (read) riding[(size_t)c].clear();
@@ -113,15 +146,20 @@ class gpuWorker {
                     if (pdamc->run_coalesced(carrier, n, Ng, group, args)) {
                         for (int o : group) {
                             N[o] = Ng;
+                            on_carrier[(size_t)o] = carrier;
                             dataready[o] = 3;
                             for (size_t k = i; k < ready.size(); ++k)
                                 if (ready[k] == o) taken[k] = 1;
                         }
                         riding[(size_t)carrier] = group;
+                        ++stats_.group_launches;
+                        stats_.grouped_vectors += group.size();
                         continue;
                     }
                 }
                 launch(sid);
+                ++stats_.single_launches;
+                on_carrier[(size_t)sid] = -1;
                 dataready[sid] = 3;
                 taken[i] = 1;
             }
@@ -166,5 +204,6 @@ class gpuWorker {
     int* ga_start;
     int* ga_stop;
     unsigned char debug;
-    int coalesce_min = 0;
+    int coalesce_min = 0, coalesce_target = 16, coalesce_linger_us = 0;
+    Stats stats_;
 };

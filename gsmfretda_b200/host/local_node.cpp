@@ -4,7 +4,10 @@
 // reference-shaped host API end to end — share_var_init's arrays, the dataready state machine,
 // the six mc calls per evaluation — and reports chi-square per vector from the fused kernel.
 //
-//   local_node <bursts.bin> <params.txt> <out.txt> [streams=4] [reSampleTimes=4] [seed] [coalesce=0]
+//   local_node <bursts.bin> <params.txt> <out.txt> [streams=4] [reSampleTimes=4] [seed] [coalesce=0] [spin=0] [target=16] [linger_us=0] [batch=1]
+//
+// batch = P > 1: every parameter thread asks for P vectors at a time and they are evaluated by ONE launch
+// (mc::set_params_batch, the batched p_ga of streamWorker.hpp); the output is the same, bit for bit.
 //
 // coalesce = K > 0: the gpuWorker thread evaluates K or more vectors that are ready at the same moment
 // with ONE launch (gpuWorker::set_coalesce); the output is the same, bit for bit.
@@ -15,6 +18,7 @@
 //   i64 burst_ad[Nph], i64 burst_dd[Nph]
 // params.txt: one vector per line: n then n*n+n floats.
 // out.txt: per vector "idx sid epoch chi2 hist[0..nb+1]".
+#include <algorithm>
 #include <chrono>
 #include <cinttypes>
 #include <cstdio>
@@ -39,11 +43,13 @@ static bool rd(FILE* f, std::vector<T>& v, size_t n) { v.resize(n); return n == 
 
 int main(int argc, char** argv)
 {
-    if (argc < 4) { std::fprintf(stderr, "usage: %s bursts.bin params.txt out.txt [streams] [R] [seed] [coalesce]\n", argv[0]); return 2; }
+    if (argc < 4) { std::fprintf(stderr, "usage: %s bursts.bin params.txt out.txt [streams] [R] [seed] [coalesce] [spin] [target] [linger_us] [batch]\n", argv[0]); return 2; }
     const int nstreams = argc > 4 ? std::atoi(argv[4]) : 4;
     const int R = argc > 5 ? std::atoi(argv[5]) : 4;
     const uint32_t seed = argc > 6 ? (uint32_t)std::strtoul(argv[6], nullptr, 10) : 1u;
     const int coalesce = argc > 7 ? std::atoi(argv[7]) : 0;
+    const int spin_looks = argc > 8 ? std::atoi(argv[8]) : 0;   // looks at the result flag before sleeping on the condition variable
+    const int batch = std::max(1, argc > 11 ? std::atoi(argv[11]) : 1);   // vectors per request of a parameter thread
 
     FILE* f = std::fopen(argv[1], "rb");
     if (!f) { std::perror(argv[1]); return 1; }
@@ -81,21 +87,37 @@ int main(int argc, char** argv)
     std::vector<std::string> lines(jobs.size());
     auto param_thread = [&](int sid) {      // the role of streamWorker::run without the socket
         for (;;) {
-            const int ji = next.fetch_add(1);
-            if (ji >= (int)jobs.size()) break;
-            { std::unique_lock<std::mutex> lck(_m[sid]);
-              s_n[sid] = jobs[ji].n; params[sid] = jobs[ji].args; ga_start[sid] = 0; ga_stop[sid] = -1;
-              pdamc.set_epoch(sid, (uint32_t)(1000 + ji));
-              dataready[sid] = 2; }
-            _cv[sid].notify_one();
-            { std::unique_lock<std::mutex> lck(_m[sid]);
-              _cv[sid].wait(lck, [&] { return dataready[sid] == 4; });
-              std::ostringstream os; os.precision(9);
-              os << ji << ' ' << sid << ' ' << 1000 + ji << ' ' << pdamc.hChi2(sid);
-              const uint64_t* h = pdamc.hHist(sid);
-              for (int i = 0; i < nbp; ++i) os << ' ' << h[i];
-              lines[ji] = os.str();
-              dataready[sid] = 0; }
+            // `batch` consecutive vectors per request (the batched p_ga of streamWorker.hpp); runs of one
+            // model inside the claim go out as one launch each, vector p with epoch 1000 + its index
+            const int j0 = next.fetch_add(batch);
+            if (j0 >= (int)jobs.size()) break;
+            const int j1 = std::min((int)jobs.size(), j0 + batch);
+            for (int ja = j0; ja < j1;) {
+                int jb = ja + 1;
+                while (jb < j1 && jobs[jb].n == jobs[ja].n && jobs[jb].args.size() == jobs[ja].args.size()) ++jb;
+                { std::unique_lock<std::mutex> lck(_m[sid]);
+                  s_n[sid] = jobs[ja].n; ga_start[sid] = 0; ga_stop[sid] = -1;
+                  params[sid].clear();
+                  for (int j = ja; j < jb; ++j) params[sid].insert(params[sid].end(), jobs[j].args.begin(), jobs[j].args.end());
+                  pdamc.set_epoch(sid, (uint32_t)(1000 + ja));
+                  dataready[sid] = 2; }
+                _cv[sid].notify_one();
+                // a short look before going to sleep: an evaluation at this scale takes tens of microseconds,
+                // a futex sleep + wake costs the gpuWorker thread more than that
+                for (int spin = 0; spin < spin_looks && __atomic_load_n(&dataready[sid], __ATOMIC_ACQUIRE) != 4; ++spin)
+                    std::this_thread::yield();
+                { std::unique_lock<std::mutex> lck(_m[sid]);
+                  _cv[sid].wait(lck, [&] { return dataready[sid] == 4; });
+                  for (int j = ja; j < jb; ++j) {
+                      std::ostringstream os; os.precision(9);
+                      os << j << ' ' << sid << ' ' << 1000 + j << ' ' << pdamc.hChi2(sid, j - ja);
+                      const uint64_t* h = pdamc.hHist(sid, j - ja);
+                      for (int i = 0; i < nbp; ++i) os << ' ' << h[i];
+                      lines[j] = os.str();
+                  }
+                  dataready[sid] = 0; }
+                ja = jb;
+            }
         }
         pdamc.workerNum--;                    // streamWorker.cpp:239-245
     };
@@ -104,7 +126,7 @@ int main(int argc, char** argv)
     for (int sid = 0; sid < streamNum; ++sid) th.emplace_back(param_thread, sid);
     gpuWorker gw(&pdamc, streamNum, &sg, opt.fret_hist_num, _m, _cv, dataready, s_n, params, ga_start, ga_stop, N, 0);
 #ifdef GSM_NODE_OWN_GPUWORKER
-    gw.set_coalesce(coalesce);
+    gw.set_coalesce(coalesce, argc > 9 ? std::atoi(argv[9]) : 16, argc > 10 ? std::atoi(argv[10]) : 0);
 #endif
     std::thread tg(&gpuWorker::run, &gw, (int)B);
     for (auto& t : th) t.join();
@@ -114,6 +136,14 @@ int main(int argc, char** argv)
     for (auto& l : lines) out << l << '\n';
     std::printf("%zu evaluations of %" PRId64 " bursts x %d repeats on %d streams in %.3f s: %.3g burst-samples/s, %.1f param-evals/s\n",
                 jobs.size(), B, R, streamNum, sec, (double)jobs.size() * B * R / sec, jobs.size() / sec);
+#ifdef GSM_NODE_OWN_GPUWORKER
+    if (coalesce > 0) {
+        const gpuWorker::Stats& st = gw.stats();
+        std::printf("coalescing: %llu passes, %llu group launches carrying %llu vectors (%.1f each), %llu single launches\n", st.passes,
+                    st.group_launches, st.grouped_vectors, st.group_launches ? (double)st.grouped_vectors / st.group_launches : 0.0,
+                    st.single_launches);
+    }
+#endif
     delete[] _m; delete[] _cv; delete[] s_n; delete[] ga_start; delete[] ga_stop; delete[] N; delete[] dataready; delete[] params;
     return 0;
 }

@@ -61,7 +61,7 @@ def test_reference_gpuworker_compiles_unchanged_against_the_shim():
     assert r.returncode == 2 and "usage" in r.stderr
 
 
-def _check_node_output(oracle, exe, tmp_path, streams, coalesce=0, P=10):
+def _check_node_output(oracle, exe, tmp_path, streams, coalesce=0, P=10, batch=1):
     w = synth.workload(4, n_bursts=1200, R=8, P=P)
     b = w.bursts()
     synth.save_bin(b, str(tmp_path / "b.bin"))
@@ -70,7 +70,8 @@ def _check_node_output(oracle, exe, tmp_path, streams, coalesce=0, P=10):
             f.write("2 " + " ".join(repr(float(x)) for x in a) + "\n")
         f.write("3 " + " ".join(repr(float(x)) for x in synth.workload(3).args[0]) + "\n")   # n changes mid-run
     r = subprocess.run([exe, str(tmp_path / "b.bin"), str(tmp_path / "p.txt"), str(tmp_path / "o.txt"), str(streams), "8", "42"]
-                       + ([str(coalesce)] if coalesce else []), capture_output=True, text=True, timeout=120)
+                       + ([str(coalesce), "0", "16", "60", str(batch)] if (coalesce or batch > 1) else []),
+                       capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stderr
     rows = [l.split() for l in open(tmp_path / "o.txt") if l.strip()]
     assert len(rows) == P + 1
@@ -104,6 +105,14 @@ def test_local_node_coalesced_launches_match_oracle(oracle, tmp_path, streams, c
     bit for bit, like the one-launch-per-stream node's (the vector of another model in the list is
     launched on its own)."""
     _check_node_output(oracle, build(), tmp_path, streams, coalesce=coalesce, P=60)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("streams,batch", [(3, 7), (2, 64)])
+def test_local_node_batched_requests_match_oracle(oracle, tmp_path, streams, batch):
+    """Every parameter thread asks for `batch` vectors at a time (the batched p_ga): one launch per
+    request through mc::set_params_batch, vector p drawn with epoch + p; same output, bit for bit."""
+    _check_node_output(oracle, build(), tmp_path, streams, batch=batch, P=60)
 
 
 @pytest.mark.gpu
