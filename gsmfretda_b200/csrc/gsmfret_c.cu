@@ -148,7 +148,8 @@ struct gsm_ctx {
     float* d_sg = nullptr;
     float* d_ohist = nullptr;
     std::vector<float> h_ohist;
-    LaunchCfg cfg{0, 0};
+    LaunchCfg cfg{0, 0, 0};
+    int occ_force = -1;   // GSM_OCC=0/1 pins the register budget of the evaluation kernel (measurements); -1: by workload
     std::atomic<uint64_t> launches{0};
     void* comm = nullptr;
     int rank = 0, world = 1;
@@ -399,6 +400,9 @@ int gsm_create(int devid, int stream_num, unsigned flags, gsm_ctx** out)
     gsm_ctx* c = new gsm_ctx();
     c->devid = devid;
     c->flags = flags;
+    if (const char* occ = getenv("GSM_OCC")) {
+        if (occ[0] == '0' || occ[0] == '1') c->occ_force = occ[0] - '0';
+    }
     for (int i = 0; i < 16; ++i) snprintf(c->uuid + 2 * i, 3, "%02x", (unsigned char)prop.uuid.bytes[i]);
     c->slots.resize(stream_num);
     for (int sid = 0; sid < stream_num; ++sid) {
@@ -804,7 +808,10 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
         CK(cudaMemcpyAsync(s.d_params, s.h_params, (size_t)s.P * sizeof(ParamRaw), cudaMemcpyHostToDevice, s.stream));
         s.params_resident = true;
     }
-    CK(launch_eval(a, c->layout, c->with_bg, c->cfg, s.stream, c->mode));
+    // the dense build (48 warps per SM) where the walk is dominated by divergent loops and dependent
+    // loads: background draws, or three and more states (pda_eval.cuh, PDA_MIN_BLOCKS_DENSE)
+    const bool dense = c->occ_force >= 0 ? c->occ_force != 0 : (c->with_bg || s.h_params[0].n >= 3);
+    CK(launch_eval(a, c->layout, c->with_bg, c->cfg, s.stream, c->mode, dense));
     c->launches += 1;
     if (c->peer_on) s.peer_seq = a.peer.seq;
     if (c->comm) {
@@ -1217,6 +1224,7 @@ int gsm_probe(gsm_ctx* c, int what, int64_t n, int ni, int nj, const uint32_t* w
     case 11: if (ni < 1 || ni > 16) return fail(GSM_EINVAL, "classes %d", ni); nw0 = 2 * N; nf0 = ni; noi = N * ni; break;
     case 12: if (ni < 1 || ni > 16) return fail(GSM_EINVAL, "classes %d", ni); nw0 = N; nf0 = ni; noi = N; break;
     case 13: nf0 = N; noi = N; break;
+    case 14: nd0 = 2 * N; nod = N; break;
     default: return fail(GSM_EINVAL, "probe kind %d", what);
     }
     ProbeArgs a{};

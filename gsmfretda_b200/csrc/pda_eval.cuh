@@ -558,11 +558,20 @@ __device__ __forceinline__ void peer_exchange_block(const EvalArgs& a, unsigned 
 // Every warp owns a copy of the parameter vector and a private histogram in shared memory,
 // draws chunks of a.chunk consecutive samples from one global ticket, and only meets the other
 // warps of its block once, at the very end (last-block finalisation).
+// Two register budgets per instantiation: 4 resident blocks per SM (64 registers: the two-state
+// walk without background is arithmetic-bound and pays for every spill) or 6 (40 registers, 48 warps
+// per SM: the background path and walks over three or more states spend their time in divergent FP64
+// loops and dependent loads, which the extra warps hide — config 5 +9 %, config 3 +4 %, config 2 -1 %,
+// profiles/r02r_variants_*.txt).  The launcher picks (launch_eval_t, `dense`).
 #ifndef PDA_MIN_BLOCKS
 #define PDA_MIN_BLOCKS 4
 #endif
-template <int kLayout, bool kBg, int kMode>
-__global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const __grid_constant__ EvalArgs a)
+#ifndef PDA_MIN_BLOCKS_DENSE
+#define PDA_MIN_BLOCKS_DENSE 6
+#endif
+template <int kLayout, bool kBg, int kMode, bool kDense>
+__global__ void __launch_bounds__(kBlock, kDense ? PDA_MIN_BLOCKS_DENSE : PDA_MIN_BLOCKS)
+pda_eval_kernel(const __grid_constant__ EvalArgs a)
 {
     constexpr int kWarps = kBlock / 32;
     __shared__ SmemParams s_params[kWarps];
@@ -787,11 +796,15 @@ __global__ void __launch_bounds__(kBlock, PDA_MIN_BLOCKS) pda_eval_kernel(const 
 // ------------------------------------------------------------------------------------
 // launch helpers, instantiated once per translation unit (kFast fixed by the unit)
 // ------------------------------------------------------------------------------------
-template <int kLayout, bool kBg, int kMode>
+// the reference-draws instantiation keeps one register budget (it is a parity tool, not a fast path)
+template <int kMode> struct HasDense { static constexpr bool value = kMode != kModeReference; };
+
+template <int kLayout, bool kBg, int kMode, bool kDense>
 static int resident_blocks(size_t dyn)
 {
     int nb = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, pda_eval_kernel<kLayout, kBg, kMode>, kBlock, dyn);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, pda_eval_kernel<kLayout, kBg, kMode, kDense && HasDense<kMode>::value>,
+                                                  kBlock, dyn);
     return nb < 1 ? 1 : nb;
 }
 
@@ -803,11 +816,13 @@ static LaunchCfg eval_launch_cfg_t(int device, int layout, bool with_bg, int nb)
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     const size_t dyn = eval_dyn_smem(nb);
-    int per;
-    if (layout == 0) per = with_bg ? resident_blocks<0, true, kMode>(dyn) : resident_blocks<0, false, kMode>(dyn);
-    else if (layout == 1) per = with_bg ? resident_blocks<1, true, kMode>(dyn) : resident_blocks<1, false, kMode>(dyn);
-    else per = with_bg ? resident_blocks<2, true, kMode>(dyn) : resident_blocks<2, false, kMode>(dyn);
-    return LaunchCfg{sms * per, kBlock};
+    int per, perd;
+#define PDA_RES(LAY, BG) (per = resident_blocks<LAY, BG, kMode, false>(dyn), perd = resident_blocks<LAY, BG, kMode, true>(dyn))
+    if (layout == 0) { if (with_bg) PDA_RES(0, true); else PDA_RES(0, false); }
+    else if (layout == 1) { if (with_bg) PDA_RES(1, true); else PDA_RES(1, false); }
+    else { if (with_bg) PDA_RES(2, true); else PDA_RES(2, false); }
+#undef PDA_RES
+    return LaunchCfg{sms * per, kBlock, sms * perd};
 }
 
 // Chunk and grid for one launch.  Large jobs: 256-sample chunks (lanes of a warp stay on the same
@@ -832,13 +847,19 @@ static inline void shape_launch(EvalArgs& a, LaunchCfg& cfg)
 }
 
 template <int kMode>
-static cudaError_t launch_eval_t(const EvalArgs& a_in, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s)
+static cudaError_t launch_eval_t(const EvalArgs& a_in, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s, bool dense)
 {
     if (a_in.nb + 2 > kMaxBins) return cudaErrorInvalidValue;
     EvalArgs a = a_in;
+    constexpr bool kHasDense = HasDense<kMode>::value;
+    if (dense) cfg.grid = cfg.grid_dense;
     shape_launch(a, cfg);
     const size_t dyn = eval_dyn_smem(a.nb);
-#define PDA_LAUNCH(LAY, BG) pda_eval_kernel<LAY, BG, kMode><<<cfg.grid, cfg.block, dyn, s>>>(a)
+#define PDA_LAUNCH(LAY, BG)                                                                   \
+    do {                                                                                      \
+        if (dense) pda_eval_kernel<LAY, BG, kMode, kHasDense><<<cfg.grid, cfg.block, dyn, s>>>(a); \
+        else pda_eval_kernel<LAY, BG, kMode, false><<<cfg.grid, cfg.block, dyn, s>>>(a);      \
+    } while (0)
     if (layout == 0) { if (with_bg) PDA_LAUNCH(0, true); else PDA_LAUNCH(0, false); }
     else if (layout == 1) { if (with_bg) PDA_LAUNCH(1, true); else PDA_LAUNCH(1, false); }
     else { if (with_bg) PDA_LAUNCH(2, true); else PDA_LAUNCH(2, false); }

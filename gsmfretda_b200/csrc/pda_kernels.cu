@@ -203,6 +203,7 @@ __global__ void pda_probe_kernel(const ProbeArgs a)
         break;
     }
     case 13: a.oi[i] = hist_index(a.f0[i], a.ni); break;
+    case 14: a.od[i] = div_pos_normal(a.d0[2 * i], a.d0[2 * i + 1]); break;   // vs the IEEE quotient
     default: break;
     }
 }
@@ -217,11 +218,11 @@ LaunchCfg eval_launch_cfg(int device, int layout, bool with_bg, int nb, int mode
                      : eval_launch_cfg_t<kModeReplay>(device, layout, with_bg, nb);
 }
 
-cudaError_t launch_eval(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s, int mode)
+cudaError_t launch_eval(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s, int mode, bool dense)
 {
-    if (mode == 2) return launch_eval_ref(a, layout, with_bg, cfg, s);
-    return mode == 1 ? launch_eval_fast(a, layout, with_bg, cfg, s)
-                     : launch_eval_t<kModeReplay>(a, layout, with_bg, cfg, s);
+    if (mode == 2) return launch_eval_ref(a, layout, with_bg, cfg, s, dense);
+    return mode == 1 ? launch_eval_fast(a, layout, with_bg, cfg, s, dense)
+                     : launch_eval_t<kModeReplay>(a, layout, with_bg, cfg, s, dense);
 }
 
 cudaError_t launch_finalize(const EvalArgs& a, cudaStream_t s)

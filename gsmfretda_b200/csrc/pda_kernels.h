@@ -100,24 +100,26 @@ struct EvalArgs {
 static_assert(sizeof(EvalArgs) <= 4096, "EvalArgs travels as a kernel parameter");
 
 struct LaunchCfg {
-    int grid;
+    int grid;        // SMs x resident blocks of the 64-register build
     int block;
+    int grid_dense;  // the same for the dense build (more resident warps, fewer registers)
 };
 
 // how many blocks to launch (persistent grid: SMs x resident blocks)
 // layout: 0 raw int64 ticks, 1 packed words scanned linearly, 2 packed words + index
 // mode: 0 replay (bit-exact draw contract), 1 normal (FP32 fast arithmetic)
 LaunchCfg eval_launch_cfg(int device, int layout, bool with_bg, int nb, int mode);
-cudaError_t launch_eval(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s, int mode);
+// dense: the build with more resident warps per SM (pda_eval.cuh, PDA_MIN_BLOCKS_DENSE)
+cudaError_t launch_eval(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s, int mode, bool dense);
 // reference-draws instantiation (pda_kernels_ref.cu) and the role of setup_kernel (gen_rand.cuh:7-25):
 // thread t starts dimension t % 20000 at offset 1234 and seeds its xor128 stream from the first word
 LaunchCfg eval_launch_cfg_ref(int device, int layout, bool with_bg, int nb);
-cudaError_t launch_eval_ref(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s);
+cudaError_t launch_eval_ref(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s, bool dense);
 cudaError_t launch_setup_ref(const unsigned long long* dv, const unsigned long long* scramble, long long NN,
                              ulonglong2* sob_state, uint4* xs_state, cudaStream_t s);
 // the normal-mode instantiation lives in its own translation unit (pda_kernels_fast.cu, fmad on)
 LaunchCfg eval_launch_cfg_fast(int device, int layout, bool with_bg, int nb);
-cudaError_t launch_eval_fast(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s);
+cudaError_t launch_eval_fast(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s, bool dense);
 // chi2 + copy-out + reset of the working histogram (used after a cross-GPU reduction)
 cudaError_t launch_finalize(const EvalArgs& a, cudaStream_t s);
 

@@ -14,9 +14,9 @@ LaunchCfg eval_launch_cfg_fast(int device, int layout, bool with_bg, int nb)
     return eval_launch_cfg_t<kModeNormal>(device, layout, with_bg, nb);
 }
 
-cudaError_t launch_eval_fast(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s)
+cudaError_t launch_eval_fast(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s, bool dense)
 {
-    return launch_eval_t<kModeNormal>(a, layout, with_bg, cfg, s);
+    return launch_eval_t<kModeNormal>(a, layout, with_bg, cfg, s, dense);
 }
 
 }  // namespace pda

@@ -40,9 +40,9 @@ LaunchCfg eval_launch_cfg_ref(int device, int layout, bool with_bg, int nb)
     return eval_launch_cfg_t<kModeReference>(device, layout, with_bg, nb);
 }
 
-cudaError_t launch_eval_ref(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s)
+cudaError_t launch_eval_ref(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s, bool dense)
 {
-    return launch_eval_t<kModeReference>(a, layout, with_bg, cfg, s);
+    return launch_eval_t<kModeReference>(a, layout, with_bg, cfg, s, dense);
 }
 
 cudaError_t launch_setup_ref(const unsigned long long* dv, const unsigned long long* scramble, long long NN,

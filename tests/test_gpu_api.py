@@ -89,6 +89,34 @@ def test_probe_binomial_poisson_bit_exact(mc1, oracle):
     assert np.array_equal(got, want)
 
 
+def test_probe_inversion_division_is_the_ieee_quotient(mc1):
+    """div_pos_normal (the hand-scheduled division of the binomial inversion loop, pda_device.cuh)
+    against numpy's IEEE double division over the domain the loop can reach — and well beyond it."""
+    rng = np.random.default_rng(14)
+    n = 2_000_000
+    # the recurrence itself: px' = ((n - X + 1) p px) / (X q)
+    nn = rng.integers(1, 3000, n).astype(np.float64)
+    X = np.minimum(rng.integers(1, 120, n), nn).astype(np.float64)
+    p = np.concatenate([rng.uniform(1e-6, 0.5, n // 2), rng.uniform(0.0, 1.0, n - n // 2).astype(np.float32) / 2])
+    px = np.exp(rng.uniform(-90.0, 0.0, n))
+    num = (nn - X + 1.0) * p * px
+    den = X * (1.0 - p)
+    keep = num > 0
+    num, den = num[keep], den[keep]
+    # wide exponents, random mantissas
+    m = 500_000
+    num = np.concatenate([num, np.ldexp(rng.uniform(1.0, 2.0, m), rng.integers(-200, 60, m))])
+    den = np.concatenate([den, np.ldexp(rng.uniform(1.0, 2.0, m), rng.integers(-40, 40, m))])
+    # mantissas next to a power of two and all-ones (the hard cases of reciprocal refinement)
+    edge = np.array([1.0, 2.0 - 2.0 ** -52, 1.0 + 2.0 ** -52, 1.5, 2.0 - 2.0 ** -51, 1.0 + 2.0 ** -51, 4.0 / 3.0])
+    en, ed = np.meshgrid(edge, edge)
+    for s in (1.0, 3.0, 1e-30, 7.0):
+        num = np.concatenate([num, en.ravel() * s]); den = np.concatenate([den, ed.ravel()])
+    k = len(num)
+    got = mc1.probe(14, k, d0=np.stack([num, den], 1).reshape(-1), out="od")
+    assert np.array_equal(got.view(np.uint64), (num / den).view(np.uint64))
+
+
 def test_batch_matches_single_evaluations(gsm, oracle):
     w = synth.workload(4, n_bursts=700, R=8, P=12)
     b = w.bursts()
