@@ -810,7 +810,10 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
     }
     // the dense build (48 warps per SM) where the walk is dominated by divergent loops and dependent
     // loads: background draws, or three and more states (pda_eval.cuh, PDA_MIN_BLOCKS_DENSE)
-    const bool dense = c->occ_force >= 0 ? c->occ_force != 0 : (c->with_bg || s.h_params[0].n >= 3);
+    // (measured, profiles/r02s_*, r02t_*: replay +9 % with background, +2 % with three states, -2 % on the
+    // two-state walk; normal mode +12 % with background, -5 % / -11 % without)
+    const bool dense = c->occ_force >= 0 ? c->occ_force != 0
+                                         : (c->with_bg || (c->mode != GSM_MODE_NORMAL && s.h_params[0].n >= 3));
     CK(launch_eval(a, c->layout, c->with_bg, c->cfg, s.stream, c->mode, dense));
     c->launches += 1;
     if (c->peer_on) s.peer_seq = a.peer.seq;

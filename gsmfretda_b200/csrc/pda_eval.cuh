@@ -126,7 +126,8 @@ __device__ __forceinline__ unsigned long long sobol_next(Lane& L)
 
 __device__ __forceinline__ uint32_t lane_g(const EvalArgs& a, const Lane& L)
 {
-    return (uint32_t)((int64_t)L.bl + a.b0 + a.g_offset);
+    // only the low 32 bits enter the draw counter: one three-input add on constant-bank operands
+    return L.bl + (uint32_t)a.b0 + (uint32_t)a.g_offset;
 }
 
 template <bool kPacked>
@@ -144,6 +145,8 @@ struct WarpCtl {
     int cur_p;                      // vector whose parameters / histogram this warp holds
     uint32_t epoch;
     int have_pending, exhausted;
+    unsigned long long span_next;   // next chunk of the span of consecutive chunks this warp drew ...
+    int span_left;                  // ... and how many of them are left (EvalArgs::span per ticket)
 };
 
 struct Window {
@@ -382,7 +385,7 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
         } else {
             if (kSobol) w.z = (uint32_t)(sobol_next(L) >> 32);
             const float rd = det_norm_icdf(w.z) * sp.v[si] + sp.rootE[si];
-            const float de = 1.0f / (1.0f + det_pow6f(rd / kR0));
+            const float de = 1.0f / (1.0f + det_pow6f(div_by_r0(rd)));
             ai = (int)binomial(L.xs, (int)f_i, (double)de, ltab);
         }
     }
@@ -615,6 +618,7 @@ pda_eval_kernel(const __grid_constant__ EvalArgs a)
     if (lane == 0) {
         wc.cur_p = -1; wc.epoch = 0u; wc.c_bl = 0u; wc.c_rep = 0u; wc.c_cnt = 0;
         wc.have_pending = 0; wc.exhausted = 0; wc.pend_item = 0ull;
+        wc.span_next = 0ull; wc.span_left = 0;
     }
     __syncwarp();
 
@@ -634,14 +638,32 @@ pda_eval_kernel(const __grid_constant__ EvalArgs a)
                     item = wc.pend_item;
                 } else {
                     if (wc.exhausted) break;
-                    item = 0;
-                    if (lane == 0) item = atomicAdd(a.counters + 0, 1ull);
-                    item = __shfl_sync(0xffffffffu, item, 0);
-                    if (item >= items) {
+                    // a ticket is a span of consecutive chunks (one chunk for a single vector; dozens
+                    // for a population, so that a warp stays on one vector instead of switching —
+                    // drain, histogram flush, parameter staging — after every chunk or two)
+                    const int span_left = wc.span_left;
+                    if (span_left > 0) {
+                        item = wc.span_next;
                         __syncwarp();
-                        if (lane == 0) wc.exhausted = 1;
+                        if (lane == 0) { wc.span_next = item + 1ull; wc.span_left = span_left - 1; }
                         __syncwarp();
-                        break;
+                    } else {
+                        item = 0;
+                        if (lane == 0) item = atomicAdd(a.counters + 0, (unsigned long long)a.span);
+                        item = __shfl_sync(0xffffffffu, item, 0);
+                        if (item >= items) {
+                            __syncwarp();
+                            if (lane == 0) wc.exhausted = 1;
+                            __syncwarp();
+                            break;
+                        }
+                        const unsigned long long rest = items - item;
+                        __syncwarp();
+                        if (lane == 0) {
+                            wc.span_next = item + 1ull;
+                            wc.span_left = (int)(rest < (unsigned long long)a.span ? rest : (unsigned long long)a.span) - 1;
+                        }
+                        __syncwarp();
                     }
                 }
                 const int p = small ? (int)((uint32_t)item / (uint32_t)chunks_per_p) : (int)(item / chunks_per_p);
@@ -841,6 +863,9 @@ static inline void shape_launch(EvalArgs& a, LaunchCfg& cfg)
     a.chunk = (int)chunk;
     a.chunk_log2 = lg;
     const long long items = ((per_p + chunk - 1) / chunk) * a.P;
+    // chunks per ticket: at least 64 tickets per warp keep the tail short
+    long long span = items / (warps * 64);
+    a.span = (int)(span < 1 ? 1 : (span > 32 ? 32 : span));
     long long blocks = (items + kBlock / 32 - 1) / (kBlock / 32);
     if (blocks < 1) blocks = 1;
     if (blocks < cfg.grid) cfg.grid = (int)blocks;

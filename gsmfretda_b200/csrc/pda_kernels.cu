@@ -183,7 +183,7 @@ __global__ void pda_probe_kernel(const ProbeArgs a)
     case 8: a.ou[i] = poisson_itr(a.w0[2 * i], a.w0[2 * i + 1], a.d0[i]); break;
     case 9: {  // drawE(e = f0[i], v = f1[i], word w0[i])
         float rd = det_norm_icdf(a.w0[i]) * a.f1[i] + kR0 * det_root6f(1.0f / a.f0[i] - 1.0f);
-        a.of[i] = 1.0f / (1.0f + det_pow6f(rd / kR0));
+        a.of[i] = 1.0f / (1.0f + det_pow6f(div_by_r0(rd)));
         break;
     }
     case 10: a.of[i] = det_logf(u01(a.w0[i])) / (-a.f0[i]); break;  // drawTau(k = f0[i])

@@ -82,6 +82,7 @@ struct EvalArgs {
     int32_t left_pad;
     int32_t chunk;             // consecutive samples per ticket (32 << k; set by the launcher)
     int32_t chunk_log2;
+    int32_t span;              // consecutive chunks a warp draws per ticket (set by the launcher)
     int32_t finalize;          // 1: the last block reduces chi2 and resets the working set
                                // 2: the same after the peer exchange (PeerArgs); 0: leave whist for a library all-reduce
     uint32_t seed;

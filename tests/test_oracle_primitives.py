@@ -169,3 +169,41 @@ def test_binomial_edge_cases(oracle):
         xs = [oracle.lib.pda_oracle_binomial(st, n, p) for _ in range(400)]
         assert all(0 <= v <= n for v in xs)
         assert abs(np.mean(xs) - n * p) < 5 * math.sqrt(n * p * (1 - p) / 400) + 1e-9
+
+
+_DIV52_C = r"""
+#include <stdio.h>
+#include <stdint.h>
+#include <string.h>
+#include <math.h>
+int main(void) {
+    const float d = 52.0f, r = 1.0f / 52.0f;
+    long bad = 0, seen = 0;
+    #pragma omp parallel for reduction(+ : bad, seen) schedule(static)
+    for (long i = 0; i < (1L << 32); ++i) {
+        uint32_t u = (uint32_t)i;
+        float x; memcpy(&x, &u, 4);
+        if (isnan(x) || isinf(x) || !(fabsf(x) > 1e-30f)) continue;
+        const float want = x / d;
+        const float q0 = x * r, rem = fmaf(-d, q0, x), q = fmaf(rem, r, q0);
+        uint32_t a, b; memcpy(&a, &want, 4); memcpy(&b, &q, 4);
+        seen++;
+        if (a != b) bad++;
+    }
+    printf("%ld %ld\n", bad, seen);
+    return 0;
+}
+"""
+
+
+def test_division_by_r0_from_its_reciprocal_is_exact(tmp_path):
+    """div_by_r0 (csrc/pda_device.cuh): RN(x / 52) from RN(1 / 52) in three operations, for EVERY float
+    beyond the 1e-30 guard — all 2^32 bit patterns are walked (a few seconds on the host cores)."""
+    import subprocess
+    src = tmp_path / "d52.c"
+    src.write_text(_DIV52_C)
+    exe = tmp_path / "d52"
+    subprocess.run(["gcc", "-O2", "-fopenmp", "-ffp-contract=off", str(src), "-o", str(exe), "-lm"], check=True)
+    bad, seen = map(int, subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split())
+    assert seen > 3_000_000_000
+    assert bad == 0
