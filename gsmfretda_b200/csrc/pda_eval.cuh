@@ -78,7 +78,10 @@ __device__ __forceinline__ int pick(const float* cum, int m, float pv)
     if (m <= 1) return 0;
     if (m == 2) return cum[0] > pv ? 0 : 1;
     if (m == 3) return cum[0] > pv ? 0 : (cum[1] > pv ? 1 : 2);
+    // at most 7 entries (kMaxStates = 8): a rolled loop — unrolled 16-fold it was 600 instructions
+    // of the hot path's code at each of its two call sites
     int r = m - 1;
+#pragma unroll 1
     for (int i = m - 2; i >= 0; --i)
         if (cum[i] > pv) r = i;
     return r;
@@ -608,7 +611,8 @@ pda_eval_kernel(const __grid_constant__ EvalArgs a)
     for (int i = lane; i < nbp; i += 32) hist[i] = 0u;
     __syncwarp();
 
-    // floor(x / R) for x < 2^16 by one multiply-high (exact while x * R < 2^32)
+    // floor(x / R) for the cursor arithmetic (x < R + 32): one multiply-high for R < 2^15 (exact while
+    // x * R < 2^32); for the larger R the quotient is 0 or 1
     const bool smallR = a.R < (1 << 15);
     const uint32_t magicR = smallR ? (uint32_t)((0x100000000ull + (uint32_t)a.R - 1u) / (uint32_t)a.R) : 0u;
 
@@ -712,7 +716,7 @@ pda_eval_kernel(const __grid_constant__ EvalArgs a)
             const int want = __popc(need);
             if (take) {
                 const uint32_t x = c_rep + (uint32_t)rank;
-                const uint32_t q = smallR ? __umulhi(x, magicR) : x / (uint32_t)a.R;
+                const uint32_t q = smallR ? __umulhi(x, magicR) : (x >= (uint32_t)a.R ? 1u : 0u);   // x < R + 32
                 lane_begin<kMode>(L, sp, a, c_bl + q, x - q * (uint32_t)a.R, wc.epoch);
                 active = true;
             }
@@ -720,7 +724,7 @@ pda_eval_kernel(const __grid_constant__ EvalArgs a)
             if (lane == 0) {
                 const int adv = want < c_cnt ? want : c_cnt;
                 const uint32_t x = c_rep + (uint32_t)adv;
-                const uint32_t q = smallR ? __umulhi(x, magicR) : x / (uint32_t)a.R;
+                const uint32_t q = smallR ? __umulhi(x, magicR) : (x >= (uint32_t)a.R ? 1u : 0u);
                 wc.c_cnt = c_cnt - adv;
                 wc.c_bl = c_bl + q;
                 wc.c_rep = x - q * (uint32_t)a.R;
