@@ -267,7 +267,7 @@ __device__ __forceinline__ void lane_save_reference(const Lane& L, const EvalArg
 // one dwell window (one trip of the reference's while loop, mc.cu:117-191)
 template <int kLayout, bool kBg, int kMode>
 __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const EvalArgs& a, uint32_t epoch,
-                                          const double2* __restrict__ ltab, const double* __restrict__ rcp)
+                                          const LogTabShared ltab, uint32_t rcp_sa)
 {
     constexpr bool kFast = kMode == kModeNormal;
     constexpr bool kSobol = kMode == kModeReference;
@@ -372,10 +372,10 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
             // one block for both channels: x / z the high word of each Poisson draw (low word 0),
             // y / w the fall-back uniforms
             const u32x4 bw = philox4x32_10(g, L.rep, L.step, kSlotBg, a.seed, epoch);
-            uint32_t sv = poisson_itr(bw.x, 0u, (double)(t_diff * a.bg_ad_rate), rcp);
+            uint32_t sv = poisson_itr_smem(bw.x, 0u, (double)(t_diff * a.bg_ad_rate), rcp_sa);
             const float bg_a = ((float)(int32_t)sv <= rf_ia) ? (float)(int32_t)sv : floorf(rf_ia * u01(bw.y));
             const float rf_id = (kGamma - kDch2Ach) * (float)win.f_id;
-            sv = poisson_itr(bw.z, 0u, (double)(t_diff * a.bg_dd_rate), rcp);
+            sv = poisson_itr_smem(bw.z, 0u, (double)(t_diff * a.bg_dd_rate), rcp_sa);
             const float bg_d = ((float)(int32_t)sv <= rf_id) ? (float)(int32_t)sv : floorf(rf_id * u01(bw.w));
             f_i = floorf(f_if - bg_d - bg_a + 0.5f);
         }
@@ -596,15 +596,20 @@ pda_eval_kernel(const __grid_constant__ EvalArgs a)
         __syncthreads();
     }
 
+    // shared address of the reciprocal table, taken once (see lds_f64)
+    const uint32_t rcp_sa = pin((uint32_t)__cvta_generic_to_shared(s_rcp));
+    const uint32_t ltab_sa = pin((uint32_t)__cvta_generic_to_shared(s_logtab));
     const int lane = threadIdx.x & 31;
     const int wid = threadIdx.x >> 5;
     const unsigned lt_mask = (1u << lane) - 1u;
     const int nbp = a.nb + 2;
     SmemParams& sp = s_params[wid];
     unsigned int* hist = s_hist_all + wid * nbp;
+    const uint32_t hist_sa = pin((uint32_t)__cvta_generic_to_shared(hist));   // the hot add goes by shared address
 
     const int64_t per_p = a.N * (int64_t)a.R;  // samples per parameter vector
-    const unsigned long long chunks_per_p = (unsigned long long)((per_p + a.chunk - 1) >> a.chunk_log2);
+    // per vector: a.big_chunks chunks of a.chunk samples, then chunks of 1 << a.tail_log2 (shape_launch)
+    const unsigned long long chunks_per_p = (unsigned long long)a.chunks_per_p;
     const unsigned long long items = chunks_per_p * (unsigned long long)a.P;
     const bool small = per_p < (1ll << 31) && items < (1ull << 32);
 
@@ -697,13 +702,18 @@ pda_eval_kernel(const __grid_constant__ EvalArgs a)
                     __syncwarp();
                 }
                 const unsigned long long c = item - (unsigned long long)p * chunks_per_p;
-                const int64_t t0 = (int64_t)(c << a.chunk_log2);
+                // guided schedule: the last stretch of a vector goes out in small chunks, so that the
+                // warps run dry within one SMALL chunk of each other (the tail of the persistent grid)
+                const bool tail = c >= (unsigned long long)a.big_chunks;
+                const int64_t t0 = tail ? (a.big_chunks << a.chunk_log2) + (int64_t)((c - (unsigned long long)a.big_chunks) << a.tail_log2)
+                                        : (int64_t)(c << a.chunk_log2);
+                const int len = tail ? (1 << a.tail_log2) : a.chunk;
                 const int64_t left = per_p - t0;
                 const int64_t bl0 = small ? (int64_t)((uint32_t)t0 / (uint32_t)a.R) : t0 / a.R;
                 __syncwarp();
                 if (lane == 0) {
                     wc.have_pending = 0;
-                    wc.c_cnt = left < a.chunk ? (int)left : a.chunk;
+                    wc.c_cnt = left < len ? (int)left : len;
                     wc.c_bl = (uint32_t)bl0;
                     wc.c_rep = (uint32_t)(t0 - bl0 * a.R);
                 }
@@ -752,7 +762,7 @@ pda_eval_kernel(const __grid_constant__ EvalArgs a)
 
         // ---- one dwell window for every active lane -------------------------------------
         if (active) {
-            lane_step<kLayout, kBg, kMode>(L, sp, a, wc.epoch, s_logtab, s_rcp);
+            lane_step<kLayout, kBg, kMode>(L, sp, a, wc.epoch, LogTabShared{ltab_sa}, rcp_sa);
             bool fin = !(L.T > L.spent);
             if (!fin && L.step >= kStepCap) {
                 atomicOr(a.counters + 2, 1ull);
@@ -776,7 +786,8 @@ pda_eval_kernel(const __grid_constant__ EvalArgs a)
                 const int bin = hist_index(e, a.nb);
                 const unsigned fm = __activemask();
                 const unsigned peers = __match_any_sync(fm, bin);
-                if (lane == __ffs(peers) - 1) atomicAdd(&hist[bin], (unsigned)__popc(peers));
+                if (lane == __ffs(peers) - 1)
+                    asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(hist_sa + (uint32_t)bin * 4u), "r"((unsigned)__popc(peers)) : "memory");
                 active = false;
             }
         }
@@ -855,7 +866,7 @@ static LaunchCfg eval_launch_cfg_t(int device, int layout, bool with_bg, int nb)
 // few bursts) on the full persistent grid.  Small jobs (the reference's own scale: a few thousand
 // bursts x 4 repeats) are latency-bound: hand out chunks as small as one sample per lane so that
 // every warp of the machine gets work, and do not launch blocks that would find the queue empty.
-static inline void shape_launch(EvalArgs& a, LaunchCfg& cfg)
+static inline void shape_launch(EvalArgs& a, LaunchCfg& cfg, bool guided)
 {
     const long long per_p = (long long)a.N * a.R;
     const long long total = per_p * a.P;
@@ -866,7 +877,32 @@ static inline void shape_launch(EvalArgs& a, LaunchCfg& cfg)
     chunk = 1ll << lg;
     a.chunk = (int)chunk;
     a.chunk_log2 = lg;
-    const long long items = ((per_p + chunk - 1) / chunk) * a.P;
+    // Guided schedule for one big vector: the last stretch (half of what the grid holds at any moment)
+    // goes out in 64-sample chunks, so that the warps run dry within ~one small chunk of each other
+    // instead of one big one: config 3 +1.5 %, config 5 +1.9 %, but config 2 -0.8 % and its normal mode
+    // -2.2 % (profiles/r02w_*, r02x_*) — so only where samples are long (`guided` = the dense build's
+    // rule).  Small chunks all the way cost up to 9 % (ticket round trips, profiles/r02t_*).
+#ifndef PDA_TAIL_LOG2
+#define PDA_TAIL_LOG2 6
+#endif
+#ifndef PDA_TAIL_DIV
+#define PDA_TAIL_DIV 2
+#endif
+    long long big = (per_p + chunk - 1) / chunk, small_n = 0;
+    a.tail_log2 = lg;
+#ifndef PDA_NO_GUIDED
+    if (guided && a.P == 1 && lg > PDA_TAIL_LOG2) {
+        const long long grid_holds = warps * chunk / PDA_TAIL_DIV;
+        const long long tail_samples = grid_holds < per_p / 8 ? grid_holds : per_p / 8;
+        const long long tc = 1ll << PDA_TAIL_LOG2;
+        big = (per_p - tail_samples) / chunk;
+        a.tail_log2 = PDA_TAIL_LOG2;
+        small_n = (per_p - big * chunk + tc - 1) / tc;
+    }
+#endif
+    a.big_chunks = big;
+    a.chunks_per_p = big + small_n;
+    const long long items = (big + small_n) * a.P;
     // chunks per ticket: at least 64 tickets per warp keep the tail short
     long long span = items / (warps * 64);
     a.span = (int)(span < 1 ? 1 : (span > 32 ? 32 : span));
@@ -882,7 +918,8 @@ static cudaError_t launch_eval_t(const EvalArgs& a_in, int layout, bool with_bg,
     EvalArgs a = a_in;
     constexpr bool kHasDense = HasDense<kMode>::value;
     if (dense) cfg.grid = cfg.grid_dense;
-    shape_launch(a, cfg);
+    // the guided tail pays where samples are long (the workloads that also take the dense build)
+    shape_launch(a, cfg, dense);
     const size_t dyn = eval_dyn_smem(a.nb);
 #define PDA_LAUNCH(LAY, BG)                                                                   \
     do {                                                                                      \

@@ -83,6 +83,9 @@ struct EvalArgs {
     int32_t chunk;             // consecutive samples per ticket (32 << k; set by the launcher)
     int32_t chunk_log2;
     int32_t span;              // consecutive chunks a warp draws per ticket (set by the launcher)
+    int32_t tail_log2;         // guided schedule: after big_chunks chunks of `chunk` samples a vector goes out in
+    int64_t big_chunks;        //   chunks of 1 << tail_log2 samples; chunks_per_p = both kinds together
+    int64_t chunks_per_p;
     int32_t finalize;          // 1: the last block reduces chi2 and resets the working set
                                // 2: the same after the peer exchange (PeerArgs); 0: leave whist for a library all-reduce
     uint32_t seed;
