@@ -580,10 +580,14 @@ __global__ void __launch_bounds__(kBlock, kDense ? PDA_MIN_BLOCKS_DENSE : PDA_MI
 pda_eval_kernel(const __grid_constant__ EvalArgs a)
 {
     constexpr int kWarps = kBlock / 32;
-    __shared__ SmemParams s_params[kWarps];
+    // per warp: the staged parameter vector and the loop's bookkeeping, one block of shared memory
+    // reached through ONE pinned 32-bit shared address (see `pin`: with 40 registers the compiler
+    // otherwise rebuilds every such pointer from %tid and the shared window base, 5-7 instructions a
+    // time, two dozen times over the loop)
+    struct WarpArea { SmemParams sp; WarpCtl ctl; };
+    __shared__ WarpArea s_warp[kWarps];
     extern __shared__ __align__(16) unsigned int s_hist_all[];  // [kWarps][nbp]; the last block reuses it for chi2 terms
     __shared__ int s_last;
-    __shared__ WarpCtl s_ctl[kWarps];
     // the {c_j, L_j} table of det_log (FP64 binomial): divergent lookups are bank conflicts here
     // instead of L1 sectors
     __shared__ double2 s_logtab[kMode == kModeNormal ? 1 : 128];
@@ -603,7 +607,9 @@ pda_eval_kernel(const __grid_constant__ EvalArgs a)
     const int wid = threadIdx.x >> 5;
     const unsigned lt_mask = (1u << lane) - 1u;
     const int nbp = a.nb + 2;
-    SmemParams& sp = s_params[wid];
+    const uint32_t warp_sa = pin((uint32_t)__cvta_generic_to_shared(&s_warp[wid]));
+    WarpArea& wa = *reinterpret_cast<WarpArea*>(__cvta_shared_to_generic(warp_sa));
+    SmemParams& sp = wa.sp;
     unsigned int* hist = s_hist_all + wid * nbp;
     const uint32_t hist_sa = pin((uint32_t)__cvta_generic_to_shared(hist));   // the hot add goes by shared address
 
@@ -623,7 +629,7 @@ pda_eval_kernel(const __grid_constant__ EvalArgs a)
 
     // warp-uniform bookkeeping lives in shared memory (volatile: every access is a broadcast
     // LDS / a lane-0 STS), which keeps it out of the per-thread register budget
-    volatile WarpCtl& wc = s_ctl[wid];
+    volatile WarpCtl& wc = wa.ctl;
     if (lane == 0) {
         wc.cur_p = -1; wc.epoch = 0u; wc.c_bl = 0u; wc.c_rep = 0u; wc.c_cnt = 0;
         wc.have_pending = 0; wc.exhausted = 0; wc.pend_item = 0ull;
