@@ -150,6 +150,7 @@ struct gsm_ctx {
     std::vector<float> h_ohist;
     LaunchCfg cfg{0, 0, 0};
     int occ_force = -1;   // GSM_OCC=0/1 pins the register budget of the evaluation kernel (measurements); -1: by workload
+    int chunk_force = 0, span_force = 0, tail_force = -1;   // GSM_CHUNK (log2), GSM_SPAN, GSM_TAIL: launch shape (tests)
     std::atomic<uint64_t> launches{0};
     void* comm = nullptr;
     int rank = 0, world = 1;
@@ -403,6 +404,9 @@ int gsm_create(int devid, int stream_num, unsigned flags, gsm_ctx** out)
     if (const char* occ = getenv("GSM_OCC")) {
         if (occ[0] == '0' || occ[0] == '1') c->occ_force = occ[0] - '0';
     }
+    if (const char* e = getenv("GSM_CHUNK")) c->chunk_force = atoi(e);
+    if (const char* e = getenv("GSM_SPAN")) c->span_force = atoi(e);
+    if (const char* e = getenv("GSM_TAIL")) c->tail_force = atoi(e) != 0;
     for (int i = 0; i < 16; ++i) snprintf(c->uuid + 2 * i, 3, "%02x", (unsigned char)prop.uuid.bytes[i]);
     c->slots.resize(stream_num);
     for (int sid = 0; sid < stream_num; ++sid) {
@@ -812,6 +816,7 @@ static int run_common(gsm_ctx* c, int N, int sid, bool upload)
     // loads: background draws, or three and more states (pda_eval.cuh, PDA_MIN_BLOCKS_DENSE)
     // (measured, profiles/r02s_*, r02t_*: replay +9 % with background, +2 % with three states, -2 % on the
     // two-state walk; normal mode +12 % with background, -5 % / -11 % without)
+    a.force_chunk_log2 = c->chunk_force; a.force_span = c->span_force; a.force_tail = c->tail_force;
     const bool dense = c->occ_force >= 0 ? c->occ_force != 0
                                          : (c->with_bg || (c->mode != GSM_MODE_NORMAL && s.h_params[0].n >= 3));
     CK(launch_eval(a, c->layout, c->with_bg, c->cfg, s.stream, c->mode, dense));

@@ -880,6 +880,7 @@ static inline void shape_launch(EvalArgs& a, LaunchCfg& cfg, bool guided)
     long long chunk = total / (warps * 4);
     int lg = 5;                                   // 32, 64, 128 or 256 samples
     while ((2ll << lg) <= chunk && (2 << lg) <= kChunkMax) ++lg;
+    if (a.force_chunk_log2 >= 5 && (1 << a.force_chunk_log2) <= kChunkMax) lg = a.force_chunk_log2;
     chunk = 1ll << lg;
     a.chunk = (int)chunk;
     a.chunk_log2 = lg;
@@ -897,6 +898,7 @@ static inline void shape_launch(EvalArgs& a, LaunchCfg& cfg, bool guided)
     long long big = (per_p + chunk - 1) / chunk, small_n = 0;
     a.tail_log2 = lg;
 #ifndef PDA_NO_GUIDED
+    if (a.force_tail >= 0) guided = a.force_tail != 0;
     if (guided && a.P == 1 && lg > PDA_TAIL_LOG2) {
         const long long grid_holds = warps * chunk / PDA_TAIL_DIV;
         const long long tail_samples = grid_holds < per_p / 8 ? grid_holds : per_p / 8;
@@ -912,6 +914,7 @@ static inline void shape_launch(EvalArgs& a, LaunchCfg& cfg, bool guided)
     // chunks per ticket: at least 64 tickets per warp keep the tail short
     long long span = items / (warps * 64);
     a.span = (int)(span < 1 ? 1 : (span > 32 ? 32 : span));
+    if (a.force_span >= 1) a.span = a.force_span;
     long long blocks = (items + kBlock / 32 - 1) / (kBlock / 32);
     if (blocks < 1) blocks = 1;
     if (blocks < cfg.grid) cfg.grid = (int)blocks;

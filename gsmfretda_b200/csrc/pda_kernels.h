@@ -86,6 +86,9 @@ struct EvalArgs {
     int32_t tail_log2;         // guided schedule: after big_chunks chunks of `chunk` samples a vector goes out in
     int64_t big_chunks;        //   chunks of 1 << tail_log2 samples; chunks_per_p = both kinds together
     int64_t chunks_per_p;
+    // launch-shape overrides for tests and measurements (GSM_CHUNK / GSM_SPAN / GSM_TAIL at gsm_create;
+    // 0 / 0 / -1: the launcher decides).  Results do not depend on any of them.
+    int32_t force_chunk_log2, force_span, force_tail;
     int32_t finalize;          // 1: the last block reduces chi2 and resets the working set
                                // 2: the same after the peer exchange (PeerArgs); 0: leave whist for a library all-reduce
     uint32_t seed;

@@ -142,6 +142,45 @@ def test_batch_matches_single_evaluations(gsm, oracle):
         assert np.array_equal(mc.hist(1, 3), oracle.hist(o["mcE"], NB))
 
 
+@pytest.mark.parametrize("env", [
+    {"GSM_CHUNK": "5", "GSM_SPAN": "3"}, {"GSM_CHUNK": "6", "GSM_SPAN": "32"}, {"GSM_CHUNK": "8", "GSM_SPAN": "2"},
+    {"GSM_CHUNK": "8", "GSM_TAIL": "1"}, {"GSM_CHUNK": "7", "GSM_TAIL": "1", "GSM_OCC": "1"},
+    {"GSM_CHUNK": "7", "GSM_TAIL": "0", "GSM_OCC": "0"}, {"GSM_OCC": "1"}, {"GSM_OCC": "0", "GSM_TAIL": "1"},
+])
+def test_results_do_not_depend_on_the_launch_shape(gsm, oracle, monkeypatch, env):
+    """Chunk size, chunks per ticket (the span a warp draws for a population), the guided tail of small
+    chunks and the register budget of the kernel build are launch-shape choices (pda_eval.cuh,
+    shape_launch): every sample, histogram and chi-square must be the same bits whatever they are —
+    for one vector (with background: both Poisson loops) and for a batch whose spans cross vector ends."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    w5 = synth.workload(5, n_bursts=1900, R=7)
+    b5 = w5.bursts()
+    with gsm.Mc(0, 1, keep_mce=True) as mc:
+        mc.set_reSampleTimes(7); mc.set_seed(11); mc.set_hist(NB, LEFT_PAD)
+        mc.init_bursts(b5)
+        mc.set_epoch(0, 3)
+        chi, h = mc.evaluate(4, w5.args[0], sid=0)
+        o = oracle.eval(b5, 4, w5.args[0], 7, 11, 3)
+        assert np.array_equal(bits(mc.hmcE(0, b5.n_bursts * 7)), bits(o["mcE"]))
+        oh = oracle.hist(o["mcE"], NB)
+        assert np.array_equal(h, oh)
+        assert np.float32(chi) == np.float32(oracle.chi2(oracle.observed_hist(b5, NB), oh, NB, 7, LEFT_PAD, 4))
+    w4 = synth.workload(4, n_bursts=411, R=5, P=9)
+    b4 = w4.bursts()
+    with gsm.Mc(0, 1, keep_mce=True) as mc:
+        mc.set_reSampleTimes(5); mc.set_seed(12); mc.set_hist(NB, LEFT_PAD)
+        mc.init_bursts(b4)
+        mc.set_epoch(0, 70)
+        mc.run_batch(b4.n_bursts, 0, 2, w4.args)
+        mc.sync(0)
+        mcE = mc.hmcE(0, 9 * b4.n_bursts * 5).reshape(9, -1)
+        for p in range(9):
+            o = oracle.eval(b4, 2, w4.args[p], 5, 12, 70 + p)
+            assert np.array_equal(bits(mcE[p]), bits(o["mcE"]))
+            assert np.array_equal(mc.hist(0, p), oracle.hist(o["mcE"], NB))
+
+
 def test_streams_are_independent_and_async(gsm, oracle):
     w2 = synth.workload(2, n_bursts=1500, R=16)
     w3 = synth.workload(3, n_bursts=1500, R=16)
