@@ -194,15 +194,30 @@ __device__ __forceinline__ Window scan_linear(const EvalArgs& a, const Lane& L, 
 // counts follow from the distance to the next acceptor / donor photon.  Exact whenever no photon
 // before `first` already reaches the new edge; otherwise (a window edge that moved backwards,
 // unsorted ticks) the photon-by-photon scan decides.
-__device__ __forceinline__ Window scan_indexed(const EvalArgs& a, const Lane& L, int64_t bin1, int thr)
+// The two loads a window search starts with, issued by the caller BEFORE the arithmetic that does not
+// depend on them (the efficiency draw of the window): the search then finds them arrived.
+struct ScanLoads { uint32_t nx, cw; };
+__device__ __forceinline__ ScanLoads scan_indexed_issue(const EvalArgs& a, const Lane& L, int thr)
+{
+    ScanLoads s{0u, 0u};
+    if (L.first < L.ph) {
+        const int64_t off = lane_off<true>(a, L);
+        s.nx = __ldg(a.nx + off + L.first);   // independent of the edge
+        const int Q = ((L.ph + 3) & ~3) - 1;
+        s.cw = __ldg(a.cw + off + cell_of(thr, L.scale, Q));
+    }
+    return s;
+}
+
+__device__ __forceinline__ Window scan_indexed(const EvalArgs& a, const Lane& L, int64_t bin1, int thr, const ScanLoads ld)
 {
     if (L.first >= L.ph) return Window{L.ph, 0, 0};
     const int64_t off = lane_off<true>(a, L);
-    const uint32_t nx = __ldg(a.nx + off + L.first);   // independent of the edge: issued first
-    const int Q = ((L.ph + 3) & ~3) - 1;
-    const uint32_t cw = __ldg(a.cw + off + cell_of(thr, L.scale, Q));
+    const uint32_t nx = ld.nx, cw = ld.cw;
     int lo = (int)(cw & 0xffffu), hi = (int)(cw >> 16);
     const int32_t* __restrict__ pm = a.pm + off;
+    // (loading the last four candidates of the bracket together instead of two or three dependent
+    // loads was tried: no gain, profiles/r03b_* — the other warps hide this latency)
     while (lo < hi) {
         const int mid = (lo + hi) >> 1;
         if (__ldg(pm + mid) >= thr) hi = mid;
@@ -264,6 +279,13 @@ __device__ __forceinline__ void lane_save_reference(const Lane& L, const EvalArg
     a.xs_state[t] = make_uint4(L.xs.s0, L.xs.s1, L.xs.s2, L.xs.s3);
 }
 
+// drawE (/root/reference/src/gen_rand.cuh:63-68) with the per-state root hoisted: E of the window from one normal word
+__device__ __forceinline__ float draw_efficiency(uint32_t word, const SmemParams& sp, int si)
+{
+    const float rd = det_norm_icdf(word) * sp.v[si] + sp.rootE[si];
+    return 1.0f / (1.0f + det_pow6f(div_by_r0(rd)));
+}
+
 // one dwell window (one trip of the reference's while loop, mc.cu:117-191)
 template <int kLayout, bool kBg, int kMode>
 __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const EvalArgs& a, uint32_t epoch,
@@ -318,6 +340,12 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
         L.fb = fabsf(f) < 9.0e18f ? truncf(f) : (float)bin1;
     }
 
+#ifdef PDA_NO_HOIST_E
+    constexpr bool kHoistE = false;
+#else
+    constexpr bool kHoistE = kMode == kModeReplay && kLayout == 2;
+#endif
+    float de_early = 0.0f;
     Window win;
     if (kLayout == 0) {
         win = scan_linear<false>(a, L, bin1, 0);
@@ -328,7 +356,16 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
         rel = rel < -(1ll << 29) + 1 ? -(1ll << 29) + 1 : rel;
         rel = rel > (1ll << 29) - 1 ? (1ll << 29) - 1 : rel;
         const int thr = bin1 <= 0 ? INT32_MIN : (int)rel * 4;
-        win = (kLayout == 2) ? scan_indexed(a, L, bin1, thr) : scan_linear<true>(a, L, bin1, thr);
+        if (kLayout == 2) {
+            const ScanLoads ld = scan_indexed_issue(a, L, thr);
+            // the efficiency of this window (if it closes on a photon: nearly always) does not depend on
+            // the search: drawn here, it runs while the index loads are in flight.  Reference-draws mode
+            // takes its word from the Sobol stream only when the window closes, so it cannot.
+            if (kHoistE) de_early = draw_efficiency(w.z, sp, si);
+            win = scan_indexed(a, L, bin1, thr, ld);
+        } else {
+            win = scan_linear<true>(a, L, bin1, thr);
+        }
     }
 
     int ai = 0;
@@ -387,8 +424,7 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
             ai = binomial_fast((int)f_i, de, w.w, g, L.rep, L.step, a.seed, epoch);
         } else {
             if (kSobol) w.z = (uint32_t)(sobol_next(L) >> 32);
-            const float rd = det_norm_icdf(w.z) * sp.v[si] + sp.rootE[si];
-            const float de = 1.0f / (1.0f + det_pow6f(div_by_r0(rd)));
+            const float de = kHoistE ? de_early : draw_efficiency(w.z, sp, si);
             ai = (int)binomial(L.xs, (int)f_i, (double)de, ltab);
         }
     }
