@@ -286,6 +286,14 @@ __device__ __forceinline__ float draw_efficiency(uint32_t word, const SmemParams
     return 1.0f / (1.0f + det_pow6f(div_by_r0(rd)));
 }
 
+__device__ __forceinline__ float draw_efficiency_fast(uint32_t word, const SmemParams& sp, int si)
+{
+    const float rd = fmaf(fast_norm_icdf(word), sp.v[si], sp.rootE[si]);
+    const float x = rd * (1.0f / kR0);
+    const float x2 = x * x;
+    return __fdividef(1.0f, fmaf(x2 * x2, x2, 1.0f));
+}
+
 // one dwell window (one trip of the reference's while loop, mc.cu:117-191)
 template <int kLayout, bool kBg, int kMode>
 __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const EvalArgs& a, uint32_t epoch,
@@ -343,7 +351,7 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
 #ifdef PDA_NO_HOIST_E
     constexpr bool kHoistE = false;
 #else
-    constexpr bool kHoistE = kMode == kModeReplay && kLayout == 2;
+    constexpr bool kHoistE = !kSobol && kLayout == 2;
 #endif
     float de_early = 0.0f;
     Window win;
@@ -361,7 +369,9 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
             // the efficiency of this window (if it closes on a photon: nearly always) does not depend on
             // the search: drawn here, it runs while the index loads are in flight.  Reference-draws mode
             // takes its word from the Sobol stream only when the window closes, so it cannot.
-            if (kHoistE) de_early = draw_efficiency(w.z, sp, si);
+            if (kHoistE) de_early = kFast ? draw_efficiency_fast(w.z, sp, si) : draw_efficiency(w.z, sp, si);
+            // (the Philox block of the background draws could go here too: measured, no gain —
+            // profiles/r03d_*)
             win = scan_indexed(a, L, bin1, thr, ld);
         } else {
             win = scan_linear<true>(a, L, bin1, thr);
@@ -417,10 +427,7 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
             f_i = floorf(f_if - bg_d - bg_a + 0.5f);
         }
         if (kFast) {
-            const float rd = fmaf(fast_norm_icdf(w.z), sp.v[si], sp.rootE[si]);
-            const float x = rd * (1.0f / kR0);
-            const float x2 = x * x;
-            const float de = __fdividef(1.0f, fmaf(x2 * x2, x2, 1.0f));
+            const float de = kHoistE ? de_early : draw_efficiency_fast(w.z, sp, si);
             ai = binomial_fast((int)f_i, de, w.w, g, L.rep, L.step, a.seed, epoch);
         } else {
             if (kSobol) w.z = (uint32_t)(sobol_next(L) >> 32);
