@@ -41,30 +41,43 @@ def split_population(P: int, world: int):
     return out
 
 
-def vector_cost(n: int, args, mean_T: float = 2.0e-3, mean_photons: float = 60.0):
-    """Rough relative cost of one burst-sample under parameter vector `args` (layout of
-    mc::set_params: E | K off-diagonal, row-major | v): photons walked plus dwell segments, the
-    latter from the stationary exit flux of K times the mean burst duration.  Only the ORDER of the
-    costs matters to deal_population."""
+def expected_jumps(n: int, args, T: float) -> float:
+    """Expected number of state changes within T of the walk mc_kernel takes under parameter vector
+    `args` (layout of mc::set_params: E | K off-diagonal, row-major | v).  The walk starts in state 0:
+    the reference compares the UNNORMALISED inflow rates with a uniform in (0, 1]
+    (drawDisIdx, /root/reference/src/gen_rand.cuh:35-50 called from mc.cu:110), so the first running sum
+    — any rate above 1/s — always wins.  E[N_T] = q^T (int_0^T e^{Gs} ds) e_0, G the generator with
+    K(row, col) = rate col -> row, q the exit rates."""
     a = np.asarray(args, dtype=np.float64)
-    k = a[n:n + n * n - n]
-    Q = np.zeros((n, n))
-    it = iter(k)
-    for i in range(n):
-        for j in range(n):
-            if i != j:
-                Q[i, j] = next(it)
-    q = Q.sum(axis=1)
-    A = (Q - np.diag(q)).T
-    A[-1, :] = 1.0
-    rhs = np.zeros(n)
-    rhs[-1] = 1.0
+    rates = iter(a[n:n + n * n - n])
+    K = np.zeros((n, n))
+    for row in range(n):
+        for col in range(n):
+            if row != col:
+                K[row, col] = next(rates)
+    q = K.sum(axis=0)
+    G = K - np.diag(q)
     try:
-        pi = np.linalg.solve(A, rhs)
+        lam, V = np.linalg.eig(G)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            small = np.abs(lam * T) < 1e-9
+            integ = np.where(small, T, np.expm1(lam * T) / np.where(small, 1.0, lam))
+        c = np.linalg.solve(V, np.eye(n)[:, 0].astype(complex))
+        val = float(np.real(q @ (V @ (integ * c))))
+        if np.isfinite(val) and val >= 0.0:
+            return val
     except np.linalg.LinAlgError:
-        pi = np.full(n, 1.0 / n)
-    flux = float(np.dot(np.clip(pi, 0.0, 1.0), q))
-    return 6.0 * mean_photons + (80.0 + 6.0 * n) * (1.0 + flux * mean_T)
+        pass
+    return float(q[0] * T)
+
+
+def vector_cost(n: int, args, mean_T: float = 2.0e-3):
+    """Relative cost of one burst-sample under parameter vector `args`: one dwell window plus one per
+    expected state change within a burst of mean duration.  Calibrated on a B200 with
+    tools/calibrate_vector_cost.py (32 vectors of the config-4 population, 1e5 bursts x 16:
+    ms = 0.1125 + 0.0491 E[jumps], rms residual 8 %; profiles/r03f_vector_cost.txt) — round 1's model
+    took the stationary exit flux, which misses that every sample starts in state 0."""
+    return 1.0 + 0.436 * expected_jumps(n, args, mean_T)
 
 
 def deal_population(costs, world: int):

@@ -85,3 +85,38 @@ def test_population_is_dealt_in_shares_of_equal_cost():
     slow = synth.pack_args([0.3, 0.7], [10, 10], [2, 2])
     fast = synth.pack_args([0.3, 0.7], [5000, 5000], [2, 2])
     assert sharding.vector_cost(2, fast) > 3 * sharding.vector_cost(2, slow)
+
+
+def test_cost_model_counts_the_jumps_the_walk_takes(oracle):
+    """sharding.expected_jumps against scipy's matrix exponential, and against the walk itself: the
+    oracle's dwell-window count per sample is 1 + the state changes within the burst, starting — as the
+    reference does — in state 0 whatever the stationary distribution says."""
+    import numpy as np
+    from scipy.linalg import expm
+    from gsmfretda_b200 import sharding, synth
+
+    def by_expm(n, args, T):
+        a = np.asarray(args, dtype=np.float64)
+        it = iter(a[n:n + n * n - n])
+        K = np.zeros((n, n))
+        for row in range(n):
+            for col in range(n):
+                if row != col:
+                    K[row, col] = next(it)
+        q = K.sum(axis=0)
+        M = np.zeros((2 * n, 2 * n))
+        M[:n, :n] = K - np.diag(q)
+        M[:n, n:] = np.eye(n)
+        return float(q @ expm(M * T)[:n, n:][:, 0])
+
+    for cfg in (2, 3, 4, 5):
+        w = synth.workload(cfg)
+        for a in w.args[:20]:
+            for T in (2e-4, 2e-3, 3e-2):
+                assert abs(sharding.expected_jumps(w.n_states, a, T) - by_expm(w.n_states, a, T)) < 1e-9 * (1 + by_expm(w.n_states, a, T))
+    w = synth.workload(4)
+    b = w.bursts(n_bursts=1500)
+    for i in (158, 770, 603, 1011):   # slow/slow, slow/fast (stationary flux ~0 but always one jump), fast/slow, fast/fast
+        steps = oracle.eval(b, 2, w.args[i], 8, 3, 0)["n_steps"]
+        want = 1.0 + float(np.mean([sharding.expected_jumps(2, w.args[i], float(T)) for T in b.T]))
+        assert abs(float(np.mean(steps)) - want) < 0.04 * want, (i, float(np.mean(steps)), want)
