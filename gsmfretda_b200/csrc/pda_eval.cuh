@@ -348,11 +348,7 @@ __device__ __forceinline__ void lane_step(Lane& L, const SmemParams& sp, const E
         L.fb = fabsf(f) < 9.0e18f ? truncf(f) : (float)bin1;
     }
 
-#ifdef PDA_NO_HOIST_E
-    constexpr bool kHoistE = false;
-#else
     constexpr bool kHoistE = !kSobol && kLayout == 2;
-#endif
     float de_early = 0.0f;
     Window win;
     if (kLayout == 0) {
@@ -932,25 +928,19 @@ static inline void shape_launch(EvalArgs& a, LaunchCfg& cfg, bool guided)
     // instead of one big one: config 3 +1.5 %, config 5 +1.9 %, but config 2 -0.8 % and its normal mode
     // -2.2 % (profiles/r02w_*, r02x_*) — so only where samples are long (`guided` = the dense build's
     // rule).  Small chunks all the way cost up to 9 % (ticket round trips, profiles/r02t_*).
-#ifndef PDA_TAIL_LOG2
-#define PDA_TAIL_LOG2 6
-#endif
-#ifndef PDA_TAIL_DIV
-#define PDA_TAIL_DIV 2
-#endif
+    constexpr int kTailLog2 = 6;   // 64-sample chunks ...
+    constexpr int kTailDiv = 2;    // ... over the last half of what the grid holds
     long long big = (per_p + chunk - 1) / chunk, small_n = 0;
     a.tail_log2 = lg;
-#ifndef PDA_NO_GUIDED
     if (a.force_tail >= 0) guided = a.force_tail != 0;
-    if (guided && a.P == 1 && lg > PDA_TAIL_LOG2) {
-        const long long grid_holds = warps * chunk / PDA_TAIL_DIV;
+    if (guided && a.P == 1 && lg > kTailLog2) {
+        const long long grid_holds = warps * chunk / kTailDiv;
         const long long tail_samples = grid_holds < per_p / 8 ? grid_holds : per_p / 8;
-        const long long tc = 1ll << PDA_TAIL_LOG2;
+        const long long tc = 1ll << kTailLog2;
         big = (per_p - tail_samples) / chunk;
-        a.tail_log2 = PDA_TAIL_LOG2;
+        a.tail_log2 = kTailLog2;
         small_n = (per_p - big * chunk + tc - 1) / tc;
     }
-#endif
     a.big_chunks = big;
     a.chunks_per_p = big + small_n;
     const long long items = (big + small_n) * a.P;
