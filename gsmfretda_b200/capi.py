@@ -93,6 +93,7 @@ SIGNATURES = {
     "gsm_probe": (C.c_int, [_ctx, C.c_int, C.c_int64, C.c_int, C.c_int, _u32p, _u32p, _f32p, _f32p,
                             _f64p, _i32p, _u32p, _f32p, _f64p, _i64p, _i32p]),
     "gsm_issue_peak": (C.c_int, [_ctx, C.c_int, C.POINTER(C.c_double)]),
+    "gsm_launch_shape": (C.c_int, [C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int64)]),
 }
 
 _lib = None

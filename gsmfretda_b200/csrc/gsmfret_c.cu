@@ -1177,6 +1177,17 @@ int gsm_peer_set_timeout(gsm_ctx* c, uint32_t ms)
     return GSM_OK;
 }
 
+int gsm_launch_shape(int64_t N, int R, int P, int resident_blocks, int guided, int64_t* out6)
+{
+    if (N < 0 || R < 1 || P < 1 || resident_blocks < 1 || !out6) return fail(GSM_EINVAL, "bad launch shape query");
+    EvalArgs a{};
+    a.N = N; a.R = R; a.P = P; a.force_tail = -1;
+    const int blocks = eval_launch_shape(a, resident_blocks, guided != 0);
+    out6[0] = a.chunk; out6[1] = a.span; out6[2] = a.tail_log2; out6[3] = a.big_chunks; out6[4] = a.chunks_per_p;
+    out6[5] = blocks;
+    return GSM_OK;
+}
+
 int gsm_issue_peak(gsm_ctx* c, int kind, double* out)
 {
     if (!c || !out || (kind != 0 && kind != 1)) return fail(GSM_EINVAL, "bad issue-peak call");

@@ -225,6 +225,13 @@ cudaError_t launch_eval(const EvalArgs& a, int layout, bool with_bg, LaunchCfg c
                      : launch_eval_t<kModeReplay>(a, layout, with_bg, cfg, s, dense);
 }
 
+int eval_launch_shape(EvalArgs& a, int resident_blocks, bool guided)
+{
+    LaunchCfg cfg{resident_blocks, kBlock, resident_blocks};
+    shape_launch(a, cfg, guided);
+    return cfg.grid;
+}
+
 cudaError_t launch_finalize(const EvalArgs& a, cudaStream_t s)
 {
     pda_finalize_kernel<<<1, kBlock, (size_t)(a.nb + 2) * sizeof(double), s>>>(a);

@@ -127,6 +127,8 @@ cudaError_t launch_setup_ref(const unsigned long long* dv, const unsigned long l
 // the normal-mode instantiation lives in its own translation unit (pda_kernels_fast.cu, fmad on)
 LaunchCfg eval_launch_cfg_fast(int device, int layout, bool with_bg, int nb);
 cudaError_t launch_eval_fast(const EvalArgs& a, int layout, bool with_bg, LaunchCfg cfg, cudaStream_t s, bool dense);
+// the launcher's ticket arithmetic on its own (gsm_launch_shape): fills a.chunk .. a.chunks_per_p, returns blocks
+int eval_launch_shape(EvalArgs& a, int resident_blocks, bool guided);
 // chi2 + copy-out + reset of the working histogram (used after a cross-GPU reduction)
 cudaError_t launch_finalize(const EvalArgs& a, cudaStream_t s);
 

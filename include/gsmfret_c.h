@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define GSM_ABI_VERSION 3
+#define GSM_ABI_VERSION 4
 
 #define GSM_OK 0
 #define GSM_EINVAL (-1)    /* bad argument */
@@ -223,7 +223,8 @@ int gsm_peer_set_timeout(gsm_ctx* ctx, uint32_t milliseconds);
 /* primitive probes: one element per input through the device code, for the unit tests
  * (role of the reference's test kernels, /root/reference/tests/GenRandTest.cu:107-135,272-287).
  * what: 0 philox, 1 logf, 2 log, 3 exp, 4 normal icdf, 5 sixth root, 6 u01, 7 binomial,
- * 8 poisson, 9 drawE, 10 drawTau, 11 multinomial, 12 categorical, 13 histogram index. */
+ * 8 poisson, 9 drawE, 10 drawTau, 11 multinomial, 12 categorical, 13 histogram index,
+ * 14 the hand-scheduled division of the binomial inversion (d0[2i] / d0[2i+1] -> od[i]). */
 int gsm_probe(gsm_ctx* ctx, int what, int64_t n, int ni, int nj, const uint32_t* w0,
               const uint32_t* w1, const float* f0, const float* f1, const double* d0,
               const int32_t* i0, uint32_t* ou, float* of, double* od, int64_t* ol, int32_t* oi);
@@ -233,6 +234,14 @@ int gsm_probe(gsm_ctx* ctx, int what, int64_t n, int ni, int nj, const uint32_t*
  * SM, timed with CUDA events.  The denominator of the issue roofline bench.py reports
  * ("INT32-only peak is to be measured by an IMAD micro-benchmark"). */
 int gsm_issue_peak(gsm_ctx* ctx, int kind, double* thread_ops_per_s);
+
+/* Host only (no device needed): how a launch of N bursts x R repeats x P vectors on a persistent grid of
+ * `resident_blocks` blocks is cut into tickets (role of the <<<grid, block>>> arithmetic of
+ * mc::set_params_buff / run_kernel, /root/reference/src/mc.cu:543,571).  guided: the tail of small chunks (what the dense
+ * build's workloads get).  out6 = chunk (samples per ticket chunk), span (chunks per ticket), log2 of the tail
+ * chunk, big chunks per vector, chunks per vector, blocks launched.  Sample t of a vector belongs to chunk
+ * c < big ? [c * chunk, (c + 1) * chunk) : [big * chunk + (c - big) << tail_log2, ...), clipped to N * R. */
+int gsm_launch_shape(int64_t N, int R, int P, int resident_blocks, int guided, int64_t* out6);
 
 #ifdef __cplusplus
 }

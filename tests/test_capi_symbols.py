@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol(gsm):
     assert not missing, missing
     import re
     declared = int(re.search(r"#define\s+GSM_ABI_VERSION\s+(\d+)", open(os.path.join(ROOT, "include", "gsmfret_c.h")).read()).group(1))
-    assert lib.gsm_abi_version() == declared >= 3     # 2: exchange stamps + shared-device flag, 3: gsm_run_coalesced
+    assert lib.gsm_abi_version() == declared >= 4     # 2: exchange stamps + shared-device flag, 3: gsm_run_coalesced, 4: gsm_launch_shape
 
 
 def test_python_binding_types_every_symbol(gsm):
@@ -59,3 +59,41 @@ def test_product_never_touches_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp", "Makefile")):
                 src = open(os.path.join(dp, f), errors="ignore").read()
                 assert "oracle_py" not in src and "pda_oracle" not in src and "libref_cpu" not in src, f
+
+
+def _shape(lib, N, R, P, blocks, guided):
+    out = (C.c_int64 * 6)()
+    assert lib.gsm_launch_shape(N, R, P, blocks, guided, out) == 0
+    return dict(zip(("chunk", "span", "tail_log2", "big", "per_p", "blocks"), [int(v) for v in out]))
+
+
+@pytest.mark.parametrize("N,R,P,blocks,guided", [
+    (7733, 4, 1, 592, 0), (100_000, 100, 1, 592, 0), (100_000, 100, 1, 888, 1), (1_000_000, 16, 1, 888, 1),
+    (1_250_000, 4, 1, 888, 1), (10_000_000, 4, 1, 888, 1), (100_000, 16, 1024, 592, 0), (100_000, 16, 128, 592, 0),
+    (1, 1, 1, 592, 1), (0, 7, 3, 592, 1), (333, 3, 9, 592, 1), (2049, 1, 1, 592, 1), (65_537, 33, 2, 888, 1),
+])
+def test_launch_shape_covers_every_sample_once(gsm, N, R, P, blocks, guided):
+    """The ticket arithmetic of the persistent grid (pda_eval.cuh, shape_launch), on the host: the chunks of a
+    vector — big ones, then the guided tail of small ones — tile [0, N*R) exactly, spans stay within
+    bounds, and no more blocks are launched than there are chunks to hand out."""
+    s = _shape(gsm.load(), N, R, P, blocks, guided)
+    per_p = N * R
+    assert s["chunk"] in (32, 64, 128, 256) and 1 <= s["span"] <= 32
+    assert 0 <= s["big"] <= s["per_p"]
+    tail = 1 << s["tail_log2"]
+    assert tail <= s["chunk"]
+    covered = 0
+    for c in range(s["per_p"]):                      # the kernel's decode of chunk c of a vector
+        t0 = c * s["chunk"] if c < s["big"] else s["big"] * s["chunk"] + (c - s["big"]) * tail
+        length = s["chunk"] if c < s["big"] else tail
+        assert t0 == covered
+        cnt = min(per_p - t0, length)
+        assert cnt > 0
+        covered += cnt
+    assert covered == per_p
+    if not (guided and P == 1):
+        assert s["big"] == s["per_p"]                # no tail without the guided schedule or for populations
+    assert 1 <= s["blocks"] <= blocks
+    assert s["blocks"] <= max(1, -(-s["per_p"] * P // 8))
+    if per_p * P >= 8 * blocks * 8 * 32:
+        assert s["blocks"] == blocks                 # big jobs fill the persistent grid
