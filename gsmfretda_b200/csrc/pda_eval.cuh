@@ -291,7 +291,7 @@ __device__ __forceinline__ float draw_efficiency_fast(uint32_t word, const SmemP
     const float rd = fmaf(fast_norm_icdf(word), sp.v[si], sp.rootE[si]);
     const float x = rd * (1.0f / kR0);
     const float x2 = x * x;
-    return __fdividef(1.0f, fmaf(x2 * x2, x2, 1.0f));
+    return fast_rcp(fmaf(x2 * x2, x2, 1.0f));
 }
 
 // one dwell window (one trip of the reference's while loop, mc.cu:117-191)
