@@ -60,6 +60,8 @@ SIGNATURES = {
     "gsm_layout": (C.c_int, [_ctx]),
     "gsm_observed_hist": (C.c_int, [_ctx, _f32p, C.c_int]),
     "gsm_set_observed_hist": (C.c_int, [_ctx, _f32p, C.c_int]),
+    # device pointers and a cudaStream_t, as integers
+    "gsm_observed_hist_static": (C.c_int, [C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p]),
     "gsm_get_max_conversion_capacity": (C.c_int, [_ctx, C.c_int]),
     "gsm_set_nstates": (C.c_int, [_ctx, C.c_int, C.c_int]),
     "gsm_set_params": (C.c_int, [_ctx, C.c_int, C.c_int, _f32p, C.c_int]),

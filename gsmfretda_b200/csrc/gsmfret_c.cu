@@ -30,6 +30,9 @@ static int fail(int code, const char* fmt, ...)
     return code;
 }
 
+// the same, for the library's other translation units (gsmfret_static.cu); not exported
+__attribute__((visibility("hidden"))) int gsm_detail_fail(int code, const char* text) { return fail(code, "%s", text); }
+
 #define CK(stmt)                                                                              \
     do {                                                                                      \
         cudaError_t e_ = (stmt);                                                              \

@@ -118,6 +118,29 @@ int gsm_layout(const gsm_ctx* ctx);
 int gsm_observed_hist(gsm_ctx* ctx, float* out, int n_bins);
 /* replace the observed histogram (burst-split runs hand every rank the global one) */
 int gsm_set_observed_hist(gsm_ctx* ctx, const float* ohist, int n_bins);
+/* The observed histogram without any allocation.  Has no counterpart in the reference (which allocates
+ * wherever it likes, mc.cu:456-521); it exists for hosts that cannot let this library do that: a process
+ * whose device memory is already committed to its own pool or arena, so that a cudaMalloc from a plug-in
+ * fails or fragments it; a generation loop or acquisition callback that cannot afford the device-wide
+ * synchronisation cudaMalloc / cudaFree bring; a worker that is handed buffers and a stream and nothing else.
+ *   d_SgDivSr  n_bursts floats   DEVICE memory of the current device (input)
+ *   d_out      n_bins floats     DEVICE memory of the current device (output: the same values
+ *                                gsm_observed_hist returns after gsm_init_data on the same SgDivSr)
+ *   stream     a cudaStream_t of the current device (NULL = the default stream); the work is enqueued
+ *              there and the call returns without waiting for it
+ * No context is needed.  The 64-bit bin counters the kernel accumulates into live in an array built into
+ * the library image, (GSM_STATIC_MAX_BINS + 2) x 8 bytes = 32 784 bytes on every GPU that loads
+ * libgsmfret.so, held until the process exits.  n_bins beyond GSM_STATIC_MAX_BINS is refused with
+ * GSM_ERANGE (use the allocating path for such an axis).  The call makes no cudaMalloc / cudaFree and uses
+ * no allocating library routine.
+ * First call on a device: it looks the array's address up once (cudaGetSymbolAddress, with that device
+ * current, under a lock) and keeps it; make this first call outside any stream capture.
+ * The array is ONE per GPU and keeps what the last call left: every call clears it first, on `stream`.
+ * Two calls whose work overlaps on the same GPU (different streams, different threads or different
+ * contexts of this process) add into the same counters and corrupt each other: order them on one stream
+ * or with events. */
+#define GSM_STATIC_MAX_BINS 4096
+int gsm_observed_hist_static(const float* d_SgDivSr, int64_t n_bursts, int n_bins, float* d_out, void* stream);
 
 /* mc::get_max_conversion_capacity()   mc.cu:326-365 : dead buffer grab in the reference; no-op, returns 1 */
 int gsm_get_max_conversion_capacity(gsm_ctx* ctx, int max_state_num);
