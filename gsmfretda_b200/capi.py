@@ -42,6 +42,7 @@ SIGNATURES = {
     "gsm_device_count": (C.c_int, []),
     "gsm_create": (C.c_int, [C.c_int, C.c_int, C.c_uint, C.POINTER(_ctx)]),
     "gsm_destroy": (None, [_ctx]),
+    "gsm_profiler": (C.c_int, [C.c_int]),
     "gsm_set_device": (C.c_int, [_ctx]),
     "gsm_stream_count": (C.c_int, [_ctx]),
     "gsm_stream": (C.c_void_p, [_ctx, C.c_int]),

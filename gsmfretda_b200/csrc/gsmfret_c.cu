@@ -4,6 +4,7 @@
 #include "../../include/gsmfret_c.h"
 #include "pda_kernels.h"
 
+#include <cuda_profiler_api.h>
 #include <dlfcn.h>
 #include <unistd.h>
 #include <atomic>
@@ -86,6 +87,9 @@ struct ResultHeader {
     unsigned long long stamp[4];   // %globaltimer of the last block: start, posted, all seen, done
     unsigned long long reserved;
 };
+
+// bench.py declares these sizes as the bytes that cross the bus per evaluation (PARAM_RAW_BYTES, RESULT_HEADER_BYTES)
+static_assert(sizeof(ParamRaw) == 616 && sizeof(ResultHeader) == 48, "update bench.py's declared copy sizes and DESIGN.md");
 
 constexpr int kDirectResultMaxP = 16;   // up to this many vectors the kernel writes results to host memory itself
 
@@ -452,6 +456,12 @@ void gsm_destroy(gsm_ctx* c)
     cudaFree(c->d_sob_dv); cudaFree(c->d_sob_sc);
     cudaGetLastError();
     delete c;
+}
+
+int gsm_profiler(int on)
+{
+    CK(on ? cudaProfilerStart() : cudaProfilerStop());
+    return GSM_OK;
 }
 
 int gsm_set_device(gsm_ctx* c)
@@ -1000,8 +1010,10 @@ const int32_t* gsm_result_steps(const gsm_ctx* c, int sid)
 int gsm_result_timing(const gsm_ctx* c, int sid, uint64_t out_ns[4])
 {
     if (!c || !out_ns || sid < 0 || sid >= (int)c->slots.size()) return fail(GSM_EINVAL, "bad timing query");
-    if (!c->slots[sid].ran) return fail(GSM_ESTATE, "no run on stream %d yet", sid);
-    const ResultHeader* h = (const ResultHeader*)c->slots[sid].h_res;
+    int pb;
+    const Slot& s = result_slot(c, sid, &pb);   // a member of a coalesced launch reads its carrier's stamps
+    if (!s.ran) return fail(GSM_ESTATE, "no run on stream %d yet", sid);
+    const ResultHeader* h = (const ResultHeader*)s.h_res;
     for (int i = 0; i < 4; ++i) out_ns[i] = h->stamp[i];
     return GSM_OK;
 }

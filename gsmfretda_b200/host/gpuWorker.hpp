@@ -112,6 +112,7 @@ class gpuWorker {
                                        std::chrono::duration_cast<std::chrono::microseconds>(now - linger_since).count() < coalesce_linger_us;
                 if (wait_more) {
                     held.clear();   // the vectors stay ready (state 2); look again
+                    std::this_thread::yield();   // the parameter threads need these mutexes to join the group
                     continue;
                 }
                 lingering = false;

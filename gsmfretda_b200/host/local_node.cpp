@@ -104,8 +104,14 @@ int main(int argc, char** argv)
                 _cv[sid].notify_one();
                 // a short look before going to sleep: an evaluation at this scale takes tens of microseconds,
                 // a futex sleep + wake costs the gpuWorker thread more than that
-                for (int spin = 0; spin < spin_looks && __atomic_load_n(&dataready[sid], __ATOMIC_ACQUIRE) != 4; ++spin)
+                // (dataready is a plain int the gpuWorker thread writes under the mutex, as in the reference: the look
+                // takes the mutex too, when it is free, instead of reading the int behind its back)
+                for (int spin = 0; spin < spin_looks; ++spin) {
+                    bool done = false;
+                    if (_m[sid].try_lock()) { done = dataready[sid] == 4; _m[sid].unlock(); }
+                    if (done) break;
                     std::this_thread::yield();
+                }
                 { std::unique_lock<std::mutex> lck(_m[sid]);
                   _cv[sid].wait(lck, [&] { return dataready[sid] == 4; });
                   for (int j = ja; j < jb; ++j) {

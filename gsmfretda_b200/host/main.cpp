@@ -256,6 +256,9 @@ int main(int argc, char* argv[])
     worker.epoch_from_idx = epoch_from_idx;
     gpuWorker gpuworker(&pdamc, streamNum, &SgDivSr, fretHistNum, _m, _cv, dataready, s_n, params, ga_start, ga_stop,
                         N, debuglevel);
+    if (coalesce > 0 && pdamc.carriers() == 0)
+        std::cout << "--coalesce is off: " << (mode == "reference" ? "reference mode evaluates one vector per launch"
+                                                                    : "per-sample outputs (--host-hist) are kept per stream") << std::endl;
     gpuworker.set_coalesce(coalesce);
     pdamc.get_max_conversion_capacity();
     std::cout << "workers created\n";

@@ -80,9 +80,9 @@ class mc {
     // one context per entry of `ids` (a GPU may be listed more than once only with
     // Options::peer_shared_device); devid / gpuuuid describe the first one
     mc(const std::vector<int>& ids, int _streamNum, unsigned char /*debug*/, std::uintmax_t /*hdf5size*/,
-       bool /*profiler*/, const Options& opt)
+       bool profiler, const Options& opt)
         : devid(ids.empty() ? 0 : ids[0]), hmcE(nullptr), s_n(nullptr), sz_burst(0), reSampleTimes(4), ctx(nullptr),
-          streamNum(0), streams(nullptr), opt_(opt)
+          streamNum(0), streams(nullptr), opt_(opt), profiler_(profiler)
     {
         gpuuuid[0] = 0;
         const unsigned flags = (opt.keep_mce ? GSM_KEEP_MCE : 0u) | (opt.force_raw64 ? GSM_FORCE_RAW64 : 0u) |
@@ -102,6 +102,7 @@ class mc {
             GSM_CHECK_RETURN(gsm_set_resample_times(c, reSampleTimes));
         }
         ctx = part_[0];
+        if (profiler_) GSM_CHECK_RETURN(gsm_profiler(1));   // cudaProfilerStart, as mc::mc does (mc.cu:207-210)
         carriers_ = opt.keep_mce ? 0 : opt.carriers;
         streamNum = gsm_stream_count(ctx) - carriers_;   // the carrier slots are not streams of the node
         workerNum.store(streamNum);
@@ -128,6 +129,7 @@ class mc {
         // peers have each other's exchange blocks mapped: release all mappings before any block goes
         if (part_.size() > 1)
             for (gsm_ctx* c : part_) gsm_peer_disconnect(c);
+        if (profiler_ && !part_.empty()) gsm_profiler(0);   // cudaProfilerStop (mc.cu:655-658)
         for (gsm_ctx* c : part_) gsm_destroy(c);
         delete[] streams;
         delete[] hmcE;
@@ -330,11 +332,12 @@ class mc {
     // stream runs by itself again.  A carrier is free again once carrierQuery says so AND its members
     // have read their results.  Lifts the per-launch driver cost off a node that evaluates many small
     // jobs (the reference's gpuWorker: one launch per stream, gpuWorker.cpp:38-87).
-    int carriers() const { return carriers_; }
+    // Reference-draws mode evaluates one vector per launch (gsm_run_coalesced answers GSM_ESTATE there): it has no carriers.
+    int carriers() const { return mode_ == GSM_MODE_REFERENCE ? 0 : carriers_; }
     bool run_coalesced(int carrier, int n, int N, const std::vector<int>& sids, const std::vector<float>& args)
     {
         const int P = (int)sids.size();
-        if (carrier < 0 || carrier >= carriers_ || P < 1 || n < 2 || (long long)args.size() != (long long)P * (n * n + n) ||
+        if (carrier < 0 || carrier >= carriers() || P < 1 || n < 2 || (long long)args.size() != (long long)P * (n * n + n) ||
             (part_.size() > 1 && P > opt_.max_batch))
             return false;
         for (size_t r = 0; r < part_.size(); ++r) {
@@ -345,7 +348,10 @@ class mc {
                 Nr = (int)(in_part < 0 ? 0 : (in_part > size ? size : in_part));
             }
             const int rc = gsm_run_coalesced(part_[r], Nr, streamNum + carrier, n, P, args.data(), sids.data());
-            if (rc == GSM_EINVAL && r == 0) return false;   // a vector the library refuses: nothing was launched
+            // A vector the library refuses (GSM_EINVAL) or a context that does not coalesce (GSM_ESTATE: reference
+            // draws, per-sample outputs): nothing was launched, the caller falls back to one launch per stream.
+            // Every part holds the same flags, mode and vectors, so a refusal can only come from part 0.
+            if ((rc == GSM_EINVAL || rc == GSM_ESTATE) && r == 0) return false;
             GSM_CHECK_RETURN(rc);
         }
         for (int sid : sids) { bad_[(size_t)sid] = 0; batch_[(size_t)sid] = 0; s_n[sid] = n; }
@@ -365,6 +371,7 @@ class mc {
     void set_mode(int mode)
     {
         for (gsm_ctx* c : part_) GSM_CHECK_RETURN(gsm_set_mode(c, mode));
+        mode_ = mode;
     }
     gsm_ctx* handle() { return ctx; }
     int gpus() const { return (int)part_.size(); }
@@ -397,6 +404,8 @@ class mc {
     std::vector<gsm_ctx*> part_;
     std::vector<int64_t> cuts_;
     int carriers_ = 0;
+    int mode_ = GSM_MODE_REPLAY;
+    bool profiler_ = false;
     std::vector<char> bad_;
     std::vector<int> batch_;
     std::vector<std::vector<float>> batch_args_;

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define GSM_ABI_VERSION 4
+#define GSM_ABI_VERSION 5
 
 #define GSM_OK 0
 #define GSM_EINVAL (-1)    /* bad argument */
@@ -63,6 +63,9 @@ int gsm_device_count(void);
 int gsm_create(int devid, int stream_num, unsigned flags, gsm_ctx** out);
 /* mc::~mc()   mc.cu:618-660  (does NOT call cudaDeviceReset: the process may own other contexts) */
 void gsm_destroy(gsm_ctx* ctx);
+/* the profiler switch of mc::mc / mc::~mc (cudaProfilerStart / cudaProfilerStop when the node runs with
+ * -P/--profiler, mc.cu:207-210,655-658): on != 0 starts, 0 stops the collection of an attached profiler */
+int gsm_profiler(int on);
 /* mc::set_gpuid()   mc.cu:199-211 : bind the calling thread to the context's device */
 int gsm_set_device(gsm_ctx* ctx);
 /* mc::getStreams(&n)   mc.cu:661-664 */
@@ -82,7 +85,7 @@ int gsm_set_seed(gsm_ctx* ctx, uint32_t seed);
  *   GSM_MODE_REPLAY  deterministic replay: explicit-rounding arithmetic, FP64 binomial on the
  *                    xor128 stream; integer counts, bins and chi-square bits equal the oracle's
  *   GSM_MODE_NORMAL  FP32 arithmetic on the hardware lg2/ex2/rcp units, FP32 binomial inversion;
- *                    same distributions (KS p > 0.01, chi-square within 1 %), about 2-3x faster
+ *                    same distributions (KS p > 0.01, chi-square within 1 %), about 1.3x faster
  * Results of either mode are a pure function of (data, parameters, seed, epoch). */
 #define GSM_MODE_REPLAY 0
 #define GSM_MODE_NORMAL 1
@@ -200,7 +203,9 @@ uint64_t gsm_result_flags(const gsm_ctx* ctx, int sid);
  * [0] it started finalising, [1] its partial histogram and arrival flags were posted to every peer,
  * [2] every peer's flag had arrived, [3] results written.  [1] = [2] = [0] without a peer exchange.
  * [2] - [1] on the rank that arrived last is the cost of the exchange itself; on the other ranks it
- * also holds the time they were ahead (skew).  Returns GSM_ESTATE before the first run. */
+ * also holds the time they were ahead (skew).  Returns GSM_ESTATE before the first run.  The stamps are
+ * those of the launch whose results the slot reads (its carrier's after gsm_run_coalesced); read them
+ * only after gsm_query returned 1 / gsm_sync — earlier they still belong to the previous run. */
 int gsm_result_timing(const gsm_ctx* ctx, int sid, uint64_t out_ns[4]);
 /* device time of the last run on the slot between its first and last enqueued operation, ms */
 float gsm_last_elapsed_ms(gsm_ctx* ctx, int sid);

@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol(gsm):
     assert not missing, missing
     import re
     declared = int(re.search(r"#define\s+GSM_ABI_VERSION\s+(\d+)", open(os.path.join(ROOT, "include", "gsmfret_c.h")).read()).group(1))
-    assert lib.gsm_abi_version() == declared >= 4     # 2: exchange stamps + shared-device flag, 3: gsm_run_coalesced, 4: gsm_launch_shape
+    assert lib.gsm_abi_version() == declared >= 4     # 2: exchange stamps + shared-device flag, 3: gsm_run_coalesced, 4: gsm_launch_shape, 5: gsm_observed_hist_static, gsm_profiler
 
 
 def test_python_binding_types_every_symbol(gsm):

@@ -107,11 +107,21 @@ def test_probe_inversion_division_is_the_ieee_quotient(mc1):
     m = 500_000
     num = np.concatenate([num, np.ldexp(rng.uniform(1.0, 2.0, m), rng.integers(-200, 60, m))])
     den = np.concatenate([den, np.ldexp(rng.uniform(1.0, 2.0, m), rng.integers(-40, 40, m))])
+    # where the loop can really go with p near 1e-16: px falls by ~1e-16 per trip until the restart, the
+    # numerator reaches ~1e-290 (2^-963) while the divisor X q stays within [0.5, 90]
+    m = 500_000
+    num = np.concatenate([num, np.ldexp(rng.uniform(1.0, 2.0, m), rng.integers(-963, -190, m))])
+    den = np.concatenate([den, rng.uniform(0.5, 90.0, m)])
+    Xs = rng.integers(1, 88, m).astype(np.float64)
+    ps = np.concatenate([rng.uniform(1e-17, 1e-15, m // 2), rng.uniform(1e-12, 1e-6, m - m // 2)])
+    num = np.concatenate([num, (rng.integers(1, 3000, m) + 1.0) * ps * np.ldexp(rng.uniform(1.0, 2.0, m), rng.integers(-910, 0, m))])
+    den = np.concatenate([den, Xs * (1.0 - ps)])
     # mantissas next to a power of two and all-ones (the hard cases of reciprocal refinement)
     edge = np.array([1.0, 2.0 - 2.0 ** -52, 1.0 + 2.0 ** -52, 1.5, 2.0 - 2.0 ** -51, 1.0 + 2.0 ** -51, 4.0 / 3.0])
     en, ed = np.meshgrid(edge, edge)
-    for s in (1.0, 3.0, 1e-30, 7.0):
+    for s in (1.0, 3.0, 1e-30, 7.0, 2.0 ** -960):
         num = np.concatenate([num, en.ravel() * s]); den = np.concatenate([den, ed.ravel()])
+    assert num.min() > 2.0 ** -1000 and np.isfinite(num).all() and (den > 0).all()
     k = len(num)
     got = mc1.probe(14, k, d0=np.stack([num, den], 1).reshape(-1), out="od")
     assert np.array_equal(got.view(np.uint64), (num / den).view(np.uint64))
@@ -356,6 +366,9 @@ def test_coalesced_launch_equals_per_stream_launches(gsm, oracle):
             assert mc.chi2v(sid).shape == (1,)
             with pytest.raises(gsm.GsmError):
                 mc.hist(sid, 1)                      # a member owns one vector of the carrier
+            # the %globaltimer stamps a member reports are its carrier's launch, not its own stale ones
+            t = mc.timing_ns(sid)
+            assert t[0] > 0 and np.array_equal(t, mc.timing_ns(7))
         # the members' epochs moved on by one: the next run of a member is its own launch again
         c2, h2 = mc.evaluate(2, w.args[0], sid=4)
         co, ho = oracle.eval_chi2(b, 2, w.args[0], 8, 5, 201, ohist, NB, LEFT_PAD)

@@ -218,3 +218,21 @@ def test_node_in_reference_mode_equals_the_reference(world, ref, oracle):
     e = ref.mc_kernel_sobol(world["b"], 2, np.array(v, np.float32), R, evals=1)[0]
     want = oracle.chi2(world["ohist"], oracle.hist(e, NB), NB, R, LEFT_PAD, 2)
     assert np.float32(chi2) == np.float32(want), (chi2, want)
+
+
+def test_coalesce_in_reference_mode_falls_back_to_one_launch_per_stream(world):
+    """--coalesce with --mode reference: reference draws are one vector per launch, so the node says that
+    coalescing is off and serves every vector with per-stream launches instead of dying on the library's
+    refusal (GSM_ESTATE) in the middle of an optimisation."""
+    srv = ParamServer(2, world["vecs"], bestfv=3.0e32)
+    try:
+        cmd = [NODE, "-u", srv.url, "-i", os.path.join(H5, "from_bin.h5"), "-s", "3", "--mode", "reference",
+               "--coalesce", "2", "--resample-times", str(R)]
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=180)
+        assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])
+        assert "--coalesce is off: reference mode" in r.stdout
+        assert sorted(srv.results) == list(range(len(world["vecs"])))
+        for i in range(len(world["vecs"])):
+            assert np.isfinite(srv.results[i]["e"]) and srv.results[i]["e"] > 0
+    finally:
+        srv.close()
