@@ -20,10 +20,10 @@ except Exception as e: print('parse failed', e)
 PY
       ;;
     launches)
-      timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${T}_launches.csv python bench.py --steps 20 --warmup 3 --no-cpu > $O/${T}_ncu_list.log 2>&1; echo "ncu list rc=$?";;
+      timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${T}_launches.csv python bench.py --steps 20 --warmup 3 --no-cpu --sustained 0 > $O/${T}_ncu_list.log 2>&1; echo "ncu list rc=$?";;
     ncu)
       M=${a2:-replay}; B=""; [ -n "$a3" ] && B="--bursts $a3"
-      timeout 900 ncu --set full --clock-control none --import-source on -k regex:pda_eval -s 3 -c 1 -o $O/${T}_full_cfg${a1}_$M -f python bench.py --cfg $a1 --only main $B --steps 3 --warmup 3 --no-cpu --mode $M > $O/${T}_ncu_full_cfg${a1}_$M.log 2>&1; echo "ncu cfg$a1 $M rc=$?";;
+      timeout 900 ncu --set full --clock-control none --import-source on -k regex:pda_eval -s 3 -c 1 -o $O/${T}_full_cfg${a1}_$M -f python bench.py --cfg $a1 --only main $B --steps 3 --warmup 3 --no-cpu --sustained 0 --mode $M > $O/${T}_ncu_full_cfg${a1}_$M.log 2>&1; echo "ncu cfg$a1 $M rc=$?";;
     variants)
       bash tools/variant_bench.sh --cfg $a1 --steps 100 --warmup 5 $a3 -- $(echo $a2 | tr ',' ' ') | tee -a $O/${T}_variants_cfg$a1.txt;;
     *) echo "unknown job $job";;

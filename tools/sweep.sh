@@ -7,7 +7,7 @@ for spec in "$@"; do
   IFS='|' read -r lib occ cfg extra <<< "$spec"
   if [ "$lib" = "default" ]; then unset GSMFRET_LIB; else export GSMFRET_LIB="$PWD/$lib"; fi
   if [ "$occ" = "-" ]; then unset GSM_OCC; else export GSM_OCC=$occ; fi
-  out=$(timeout 300 python bench.py --no-cpu --only main --cfg $cfg --steps 100 --warmup 5 $extra 2>/tmp/sw.err | tail -1)
+  out=$(timeout 300 python bench.py --no-cpu --sustained 0 --only main --cfg $cfg --steps 100 --warmup 5 $extra 2>/tmp/sw.err | tail -1)
   echo "$out" | python -c "
 import sys,json
 try:

@@ -5,7 +5,7 @@ while [ $# -gt 0 ] && [ "$1" != "--" ]; do args+=("$1"); shift; done
 shift
 for v in "$@"; do
   if [ "$v" = "default" ]; then unset GSMFRET_LIB; else export GSMFRET_LIB="$PWD/$v"; fi
-  out=$(python bench.py --no-cpu "${args[@]}" 2>/tmp/vb.err | tail -1)
+  out=$(python bench.py --no-cpu --sustained 0 "${args[@]}" 2>/tmp/vb.err | tail -1)
   echo "$out" | python -c "
 import sys,json
 try:
