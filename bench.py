@@ -380,7 +380,9 @@ class Env:
         mc.set_seed(SEED)
         mc.set_hist(NB, LEFT_PAD)
         mc.set_mode(self.MODES[mode])
-        mc.init_bursts(b, g_offset=g_offset)
+        t_init = time.perf_counter()
+        mc.init_bursts(b, g_offset=g_offset)      # returns when the packed, indexed arrays are resident
+        mc.init_ms = 1e3 * (time.perf_counter() - t_init)
         if split and self.world > 1:
             if collective == "nccl":
                 idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
@@ -602,6 +604,7 @@ def time_leg(env, cfg, w, b, kind, steps, warmup, mode, collective, g_offset=0, 
 
     peak_imad, peak_ffma = mc.issue_peak(0), mc.issue_peak(1)
     packed = mc.is_packed()
+    init_ms = mc.init_ms
     mc.close()
 
     per_rank = env.gather([dev_ms / steps, clk.get("sm_mhz") or 0.0, clk.get("power_w") or 0.0, 1.0 if clk["reasons"] else 0.0])
@@ -659,6 +662,9 @@ def time_leg(env, cfg, w, b, kind, steps, warmup, mode, collective, g_offset=0, 
         "clocks": clk,
         "chi2": float(chi2_last),
     }
+    out["init_ms"] = {"value": init_ms, "what": "gsm_init_data on this rank's bursts, host wall clock: H2D of the raw int64 "
+                      "arrays from pageable memory, the pack and index kernels, the observed histogram (one-time, mc::init_data_gpu)",
+                      "bursts": B, "photons": int(b.n_photons)}
     if other:
         out["other_mode"] = other
     if sustained:
