@@ -51,6 +51,21 @@ def test_no_cpu_fallback(gsm):
         gsm.Mc(0, 2)
 
 
+def test_static_entry_point_has_no_cpu_fallback_either(gsm):
+    """gsm_observed_hist_static on a box without a GPU: argument checks first (GSM_ERANGE beyond the built-in
+    scratch, whatever the box), then a loud GSM_ENODEVICE — the pointers are never touched on the host."""
+    import torch
+    lib = gsm.load()
+    fake_in, fake_out = C.c_void_p(0x1000), C.c_void_p(0x2000)
+    assert lib.gsm_observed_hist_static(fake_in, 10, 4097, fake_out, None) == -6      # GSM_ERANGE
+    assert b"GSM_STATIC_MAX_BINS" in lib.gsm_last_error()
+    assert lib.gsm_observed_hist_static(fake_in, 10, 200, None, None) == -1           # GSM_EINVAL
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    assert lib.gsm_observed_hist_static(fake_in, 10, 200, fake_out, None) == -3       # GSM_ENODEVICE
+    assert b"no CPU path" in lib.gsm_last_error()
+
+
 def test_product_never_touches_the_oracle():
     """Nothing under gsmfretda_b200/ may import, link or call oracle/."""
     pkg = os.path.join(ROOT, "gsmfretda_b200")
